@@ -1,0 +1,73 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU oracle for the blob mobility product.
+
+ctypes binding of oracle/mobility_oracle.c (a plain-C restatement of
+/root/reference/mobility/mobility_numba.py + the wrappers of mobility.py).
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs may import this package.  The product
+(rigidmultiblobswall_b200/) never does.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libmobility_oracle.so")
+BLOCKS = {"UF": 0, "UT": 1, "WF": 2, "WT": 3}
+_lib = None
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "mobility_oracle.c")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s", "-B"])
+    return _SO
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = ctypes.CDLL(_SO)
+        dp = ctypes.POINTER(ctypes.c_double)
+        _lib.rmb_oracle_block.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_long, dp, dp,
+                                          ctypes.c_double, ctypes.c_double, dp,
+                                          ctypes.c_long, ctypes.c_long, dp]
+        _lib.rmb_oracle_wall_wrap.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_long, dp, dp,
+                                              ctypes.c_double, ctypes.c_double, dp,
+                                              ctypes.c_long, ctypes.c_long, dp]
+        _lib.rmb_oracle_threads.restype = ctypes.c_int
+    return _lib
+
+
+def _p(x):
+    return x.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+
+
+def threads():
+    return int(lib().rmb_oracle_threads())
+
+
+def mobility_product(block, wall, r_vectors, vec, eta, a, periodic_length=None,
+                     in_plane=False, targets=None):
+    """block in UF/UT/WF/WT; wall in {'single_wall','no_wall'}.
+
+    Mirrors mobility.py's `<wall>_mobility_<block>_numba(r, vec, eta, a,
+    periodic_length=L)` including the height clamp and damping B for the wall
+    forms.  targets=(begin, end) restricts the computed rows (bounded sample).
+    """
+    r = np.ascontiguousarray(np.asarray(r_vectors, dtype=np.float64).reshape(-1, 3))
+    v = np.ascontiguousarray(np.asarray(vec, dtype=np.float64).reshape(-1, 3))
+    n = r.shape[0]
+    L = np.zeros(3) if periodic_length is None else np.ascontiguousarray(periodic_length, dtype=np.float64)
+    b, e = (0, n) if targets is None else targets
+    out = np.empty(3 * (e - b))
+    if wall == "single_wall":
+        lib().rmb_oracle_wall_wrap(BLOCKS[block], int(in_plane), n, _p(r), _p(v), eta, a, _p(L), b, e, _p(out))
+    elif wall == "no_wall":
+        assert not in_plane
+        lib().rmb_oracle_block(BLOCKS[block], 0, n, _p(r), _p(v), eta, a, _p(L), b, e, _p(out))
+    else:
+        raise ValueError(wall)
+    return out

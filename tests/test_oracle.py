@@ -1,0 +1,38 @@
+"""Pins oracle/mobility_oracle.c against the reference's numba outputs
+(tests/golden/mf_golden.npz, made by tests/golden/make_golden.py)."""
+import numpy as np
+import pytest
+
+import oracle
+
+
+def _cases():
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "mf_golden.npz"))
+    return [str(c) for c in g["cases"]]
+
+
+def relerr(x, ref):
+    return np.linalg.norm(x - ref) / np.linalg.norm(ref)
+
+
+@pytest.mark.parametrize("case", _cases())
+def test_oracle_matches_reference_numba(golden, case):
+    cloud, lname, wall, blk = case.split("/")
+    r, v = golden[f"{cloud}/r"], golden[f"{cloud}/v"]
+    a, eta = golden[f"{cloud}/a_eta"]
+    L = golden[f"{cloud}/L_{lname}"]
+    in_plane = wall == "in_plane"
+    out = oracle.mobility_product(blk, "single_wall" if in_plane else wall, r, v, eta, a, L, in_plane=in_plane)
+    ref = golden[case]
+    assert out.shape == ref.shape
+    # numba is fastmath (not bit-reproducible); 1e-13 norm-wise is an order below the 1e-12 bar
+    assert relerr(out, ref) < 1e-13
+
+
+def test_oracle_target_subset(golden):
+    r, v = golden["dense/r"], golden["dense/v"]
+    a, eta = golden["dense/a_eta"]
+    full = oracle.mobility_product("UF", "single_wall", r, v, eta, a)
+    part = oracle.mobility_product("UF", "single_wall", r, v, eta, a, targets=(17, 60))
+    assert np.array_equal(full[3 * 17:3 * 60], part)
