@@ -1,0 +1,131 @@
+// mf_core.cuh -- record layout, image wrap and the per-pair dispatch shared by
+// the CUDA kernels (rmb_mobility.cu) and the host-side algebra check
+// (tests/host_pair_harness.cpp, g++ -DRMB_HOST_ONLY).
+#pragma once
+#include "pair_math.cuh"
+
+namespace rmb {
+
+enum Block { UF = 0, UT = 1, WF = 2, WT = 3, UF_UT = 4 };
+
+// One packed source blob in HBM / shared memory: position followed by NV
+// 3-vectors (NV = 1: force or torque; NV = 2: force and torque/a for the
+// fused UF+UT product).  48 B (fp64, NV=1) = three 16-byte shared-memory
+// broadcasts per pair.  Positions are in units of a for the open-boundary
+// kernels and unscaled for the pseudo-periodic ones (the wrap is done in the
+// caller's length unit, exactly where the reference does it).
+template <typename T, int NV>
+struct alignas(8) SrcRec {
+  T x, y, z;
+  T v[3 * NV];
+};
+
+// Pseudo-periodic parameters (host-filled).  L[d] <= 0: not periodic in d.
+template <typename T>
+struct Periodic {
+  T L[3];
+  T invL[3];
+  int per[3];
+  int nbox;  // 3^(number of periodic directions)
+};
+
+// mobility_numba.py:184-192:  r -= int(r/L + 0.5*sign(r)) * L ; r += box*L.
+// int() truncates toward zero; copysign(0.5, 0) = 0.5 truncates to 0 like
+// sign(0) = 0 does.
+template <typename T>
+RMB_HD T wrap_shift(T r, T L, T invL, T shift)
+{
+#if defined(RMB_HOST_ONLY)
+  const T n = std::trunc(RMB_FMA(r, invL, std::copysign(T(0.5), r)));
+#else
+  const T n = trunc(RMB_FMA(r, invL, copysign(T(0.5), r)));
+#endif
+  return RMB_FMA(-n, L, r) + shift;
+}
+
+// Decode image box index b in [0, nbox) into the shift vector (box * L).
+// Ordering: x slowest, z fastest, each periodic direction running -1, 0, +1
+// (same nesting as the reference loops).  central = all components zero.
+template <typename T>
+RMB_HD void box_shift(const Periodic<T>& P, int b, T& sx, T& sy, T& sz, bool& central)
+{
+  int k[3];
+  for (int d = 2; d >= 0; --d) {
+    if (P.per[d]) { k[d] = (b % 3) - 1; b /= 3; } else k[d] = 0;
+  }
+  sx = T(k[0]) * P.L[0]; sy = T(k[1]) * P.L[1]; sz = T(k[2]) * P.L[2];
+  central = (k[0] == 0) && (k[1] == 0) && (k[2] == 0);
+}
+
+// Target-side loop invariants.
+template <typename T>
+struct Target {
+  T x, y, z;  // same unit as the source records
+  T h;        // z / a
+};
+
+// Geometry of one pair.  PERIODIC: positions unscaled, wrap, then 1/a.
+template <typename T, bool WALL, bool PERIODIC>
+RMB_HD void pair_geometry(const Target<T>& t, T xj, T yj, T zj, const Periodic<T>& P, T sx, T sy, T sz, T inva,
+                          PairGeom<T>& g, T& r2, T& rxy2)
+{
+  g.rx = t.x - xj; g.ry = t.y - yj; g.rz = t.z - zj;
+  if (PERIODIC) {
+    if (P.per[0]) g.rx = wrap_shift(g.rx, P.L[0], P.invL[0], sx);
+    if (P.per[1]) g.ry = wrap_shift(g.ry, P.L[1], P.invL[1], sy);
+    if (P.per[2]) g.rz = wrap_shift(g.rz, P.L[2], P.invL[2], sz);
+    g.rx *= inva; g.ry *= inva; g.rz *= inva;
+    if (WALL) {
+      g.Rz = (t.z + zj) * inva;       // no wrap, no shift (mobility_numba.py:242)
+      g.h = zj * inva;
+    }
+  } else {
+    if (WALL) {
+      g.Rz = t.z + zj;
+      g.h = zj;
+    }
+  }
+  rxy2 = RMB_FMA(g.ry, g.ry, g.rx * g.rx);
+  r2 = RMB_FMA(g.rz, g.rz, rxy2);
+}
+
+// One pair, one block.  v = the record's vectors (already zeroed by the
+// caller for the self pair, whose geometry it also made finite).  g.h is the
+// SOURCE height; ht is the TARGET height, which the transposed wall term of
+// UT uses instead (mobility_numba.py:651).
+template <typename T, int BLOCK, bool WALL>
+RMB_HD void pair_apply(const PairGeom<T>& g, T ht, const T* v, bool any_near, T r2, T rxy2, T& ux, T& uy, T& uz)
+{
+  if (BLOCK == UF || BLOCK == UF_UT) pair_uf<T, WALL>(g, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
+  if (BLOCK == WF) pair_wf<T, WALL>(g, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
+  if (BLOCK == WT) pair_wt<T, WALL>(g, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
+  if (BLOCK == UT || BLOCK == UF_UT) {
+    PairGeom<T> gt = g;
+    gt.h = ht;
+    const T* t = (BLOCK == UF_UT) ? v + 3 : v;   // fused: second vector is torque / a
+    pair_ut<T, WALL>(gt, t[0], t[1], t[2], any_near, r2, rxy2, ux, uy, uz);
+  }
+}
+
+// Closed-form self term (i == j in the central box), h = z_i/a, v = own vectors.
+template <typename T, int BLOCK, bool WALL>
+RMB_HD void self_apply(T h, const T* v, T& ux, T& uy, T& uz)
+{
+  if (BLOCK == UF || BLOCK == UF_UT) self_uf<T, WALL>(h, v[0], v[1], v[2], ux, uy, uz);
+  if (BLOCK == UT && WALL) self_ut<T>(h, v[0], v[1], ux, uy);
+  if (BLOCK == WF && WALL) self_wf<T>(h, v[0], v[1], ux, uy);
+  if (BLOCK == WT) self_wt<T, WALL>(h, v[0], v[1], v[2], ux, uy, uz);
+  if (BLOCK == UF_UT && WALL) self_ut<T>(h, v[3], v[4], ux, uy);
+}
+
+// Normalisation 1/(8 pi eta a^k), k = 1 (UF, fused), 2 (UT, WF), 3 (WT).
+inline double block_norm(int block, double eta, double a)
+{
+  const double pi = 3.14159265358979323846;
+  double n = 1.0 / (8.0 * pi * eta * a);
+  if (block == UT || block == WF) n = 1.0 / (8.0 * pi * eta * a * a);
+  if (block == WT) n = 1.0 / (8.0 * pi * eta * a * a * a);
+  return n;
+}
+
+}  // namespace rmb

@@ -1,0 +1,309 @@
+// pair_math.cuh -- per-pair arithmetic of the blob mobility blocks.
+//
+// What each function computes is fixed by the reference
+// (/root/reference/mobility/mobility_numba.py, lines cited per function); HOW
+// it is computed is not: every block is rewritten as "coefficients times
+// vectors" so that no 3x3 matrix is formed, there is no division and no sqrt
+// (one reciprocal-square-root per distance, MUFU.RSQ64H + one cubic
+// correction), and h_hat = h/Rz never appears on its own (h_hat*ez = h/|R|).
+//
+// All lengths are in units of the blob radius a.  Accumulators are NOT
+// normalised: the 1/(8 pi eta a^k) factor is applied once per target.
+// The self pair (i == j, central box) is never passed to these functions;
+// its closed-form term is added once per target by self_term_*().
+//
+// The file is plain C++ templates: it compiles under nvcc (device code) and,
+// for tests/test_pair_math_host.py only, under g++ (RMB_HOST_ONLY) so that the
+// restructured algebra can be checked against the oracle without a GPU.
+#pragma once
+
+#if defined(RMB_HOST_ONLY)
+#include <cmath>
+#define RMB_HD inline
+#define RMB_FMA(a, b, c) std::fma((a), (b), (c))
+#else
+#define RMB_HD __device__ __forceinline__
+#define RMB_FMA(a, b, c) fma((a), (b), (c))
+#endif
+
+namespace rmb {
+
+// ---------------------------------------------------------------- rsqrt ----
+#if defined(RMB_HOST_ONLY)
+// Host emulation of the device sequence: a seed with ~2^-20 relative error
+// (what rsqrt.approx.ftz.f64 guarantees) followed by the same correction.
+RMB_HD double rsqrt_seed(double x) { return (double)(float)(1.0 / std::sqrt(x)) * (1.0 + 9.0e-7); }
+RMB_HD float rsqrt_fast(float x) { return 1.0f / std::sqrt(x); }
+#else
+RMB_HD double rsqrt_seed(double x)
+{
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));  // MUFU.RSQ64H
+  return y;
+}
+RMB_HD float rsqrt_fast(float x) { return rsqrtf(x); }  // MUFU.RSQ
+#endif
+
+// 1/sqrt(x) to < 1 ulp-ish: y0(1 + e/2 + 3e^2/8), e = 1 - x y0^2 (cubic
+// convergence: seed error 2^-20 -> 5/16 e^3 ~ 2^-58).  5 FP64 instructions.
+RMB_HD double rsqrt_full(double x)
+{
+  const double y0 = rsqrt_seed(x);
+  const double t = x * y0;
+  const double e = RMB_FMA(-t, y0, 1.0);
+  const double p = RMB_FMA(0.375, e, 0.5);
+  return RMB_FMA(y0, p * e, y0);
+}
+RMB_HD float rsqrt_full(float x) { return rsqrt_fast(x); }
+
+// "is r2 < 4" without touching the FP64 pipe: compare the high word.
+#if defined(RMB_HOST_ONLY)
+RMB_HD bool lt4(double r2) { return r2 < 4.0; }
+RMB_HD bool lt4(float r2) { return r2 < 4.0f; }
+#else
+RMB_HD bool lt4(double r2) { return __double2hiint(r2) < 0x40100000; }
+RMB_HD bool lt4(float r2) { return r2 < 4.0f; }
+#endif
+
+// Geometry of one pair, lengths / a.  (rx,ry,rz) = x_i - x_j after the image
+// wrap; Rz = z_i + z_j and h (height of source, or of target for UT) are
+// only used by the wall corrections.
+template <typename T>
+struct PairGeom {
+  T rx, ry, rz, Rz, h;
+};
+
+// ------------------------------------------------------------------- UF ----
+// Free-space RPY translation-translation (mobility_numba.py:199-239):
+//   far  (r > 2):  [ (1 + 2/(3r^2)) I + (1 - 2/r^2) rr/r^2 ] / r
+//   near (r <= 2): 4/3 [ (1 - 9r/32) I + 3/(32 r) rr ]
+// Wall correction (:242-276), Swan & Brady fact1..5 with e = R/|R|,
+// R = (rx, ry, Rz), g = h_hat*ez = h/|R|:
+//   u += fact1 f + e (fact2 (e.f) + fact3 f_z) + z^ (fact4 (e.f) + fact5 f_z)
+// ANY_NEAR: warp-uniform flag "some lane of this warp has r2 < 4" -- the near
+// coefficients are only evaluated when it is set.
+template <typename T, bool WALL>
+RMB_HD void pair_uf(const PairGeom<T>& p, T fx, T fy, T fz, bool any_near, T r2, T rxy2, T& ux, T& uy, T& uz)
+{
+  const T s = RMB_FMA(p.ry, fy, p.rx * fx);
+  const T invr = rsqrt_full(r2);
+  const T invr2 = invr * invr;
+  const T rf = RMB_FMA(p.rz, fz, s);
+  const T invr3 = invr2 * invr;
+  T A = RMB_FMA(T(2.0 / 3.0), invr3, invr);          // (1 + 2/(3 r^2)) / r
+  const T rfi = rf * invr3;
+  T B = RMB_FMA(T(-2.0), invr2 * rfi, rfi);          // (1 - 2/r^2) (r.f) / r^3
+  if (any_near) {
+    const T r = r2 * invr;
+    const T An = RMB_FMA(T(-0.375), r, T(4.0 / 3.0));
+    const T Bn = (T(0.125) * invr) * rf;
+    const bool near = lt4(r2);
+    A = near ? An : A;
+    B = near ? Bn : B;
+  }
+  ux = RMB_FMA(A, fx, ux); uy = RMB_FMA(A, fy, uy); uz = RMB_FMA(A, fz, uz);
+  ux = RMB_FMA(B, p.rx, ux); uy = RMB_FMA(B, p.ry, uy); uz = RMB_FMA(B, p.rz, uz);
+  if (WALL) {
+    const T R2 = RMB_FMA(p.Rz, p.Rz, rxy2);
+    const T q = rsqrt_full(R2);
+    const T q2 = q * q;
+    const T ez = p.Rz * q;
+    const T g = p.h * q;
+    const T ez2 = ez * ez;
+    const T d = ez - g;
+    const T w = g * d;
+    const T Rf = RMB_FMA(p.Rz, fz, s);
+    const T ef = Rf * q;
+    // m_k = fact_k / q as polynomials in q2 (Horner)
+    T m1 = RMB_FMA(T(-10.0 / 3.0), ez2, T(2.0 / 3.0));
+    m1 = RMB_FMA(m1, q2, RMB_FMA(T(2.0), ez2, T(-2.0 / 3.0)));
+    m1 = RMB_FMA(m1, q2, RMB_FMA(T(-2.0), w, T(-1.0)));
+    T m2 = RMB_FMA(T(70.0 / 3.0), ez2, T(-10.0 / 3.0));
+    m2 = RMB_FMA(m2, q2, RMB_FMA(T(-10.0), ez2, T(2.0)));
+    m2 = RMB_FMA(m2, q2, RMB_FMA(T(6.0), w, T(-1.0)));
+    T m3 = RMB_FMA(T(-140.0 / 3.0), ez2, T(40.0 / 3.0));
+    m3 = RMB_FMA(m3, q2, RMB_FMA(T(20.0), ez2, T(-4.0)));
+    m3 = (m3 * q2) * ez;
+    m3 = RMB_FMA(g, RMB_FMA(T(-12.0), ez * d, T(2.0)), m3);
+    const T q4 = q2 * q2;
+    const T m4 = RMB_FMA(T(-20.0 / 3.0), ez * q4, g + g);
+    T m5 = RMB_FMA(T(20.0), ez2, T(-8.0 / 3.0));
+    m5 = RMB_FMA(T(-4.0), ez2, m5 * q2);
+    m5 = RMB_FMA(T(-4.0), g * g, m5 * q2);
+    const T f1 = m1 * q;
+    const T P = RMB_FMA(m2, ef, m3 * fz) * q2;        // (fact2 (e.f) + fact3 fz) / |R|
+    const T Z = RMB_FMA(m4, ef, m5 * fz) * q;         // fact4 (e.f) + fact5 fz
+    ux = RMB_FMA(f1, fx, ux); uy = RMB_FMA(f1, fy, uy); uz = RMB_FMA(f1, fz, uz);
+    ux = RMB_FMA(P, p.rx, ux); uy = RMB_FMA(P, p.ry, uy); uz = RMB_FMA(P, p.Rz, uz);
+    uz += Z;
+  }
+}
+
+// Self term of UF (:203-208, :246-252); h = z_i / a (clamped), f = own force.
+template <typename T, bool WALL>
+RMB_HD void self_uf(T h, T fx, T fy, T fz, T& ux, T& uy, T& uz)
+{
+  T mxx = T(4.0 / 3.0), mzz = T(4.0 / 3.0);
+  if (WALL) {
+    const T iz = T(1.0) / h;
+    const T iz3 = iz * iz * iz;
+    const T iz5 = iz3 * iz * iz;
+    mxx += -(T(9.0) * iz - T(2.0) * iz3 + iz5) / T(12.0);
+    mzz += -(T(9.0) * iz - T(4.0) * iz3 + iz5) / T(6.0);
+  }
+  ux = RMB_FMA(mxx, fx, ux); uy = RMB_FMA(mxx, fy, uy); uz = RMB_FMA(mzz, fz, uz);
+}
+
+// -------------------------------------------------------------- UT / WF ----
+// Free-space translation-rotation coupling (mobility_numba.py:611-648,
+// :1001-1035): antisymmetric, M v = k (v x r) with k = 1/r^3 (r >= 2) or
+// (1 - 3r/8)/2 (r < 2).
+// Wall corrections: WF (:1037-1066) uses e = (rx,ry,Rz)/|R| and the SOURCE
+// height; UT (:648-679) is the transposed call: e = (-rx,-ry,Rz)/|R| and the
+// TARGET height.  With g = h/|R| (= h_hat*ez):
+//   f1 = q^2, f2 = 12 g ez q^2 + 2(1-10ez^2) q^4,
+//   f3 = -6 g q^2 + 10 ez q^4, f4 = -2 g q^2 + 2 ez q^4
+template <typename T>
+RMB_HD T coupling_k(T r2, bool any_near)
+{
+  const T invr = rsqrt_full(r2);
+  T k = invr * invr * invr;
+  if (any_near) {
+    const T kn = RMB_FMA(T(-0.1875), r2 * invr, T(0.5));
+    k = lt4(r2) ? kn : k;
+  }
+  return k;
+}
+
+template <typename T>
+struct CouplingWall {
+  T ex, ey, ez, f1, f12, f3, f1ez4;  // f12 = f1+f2, f1ez4 = f1*ez + f4
+};
+
+template <typename T>
+RMB_HD CouplingWall<T> coupling_wall(T rx, T ry, T Rz, T h, T rxy2)
+{
+  CouplingWall<T> c;
+  const T q = rsqrt_full(RMB_FMA(Rz, Rz, rxy2));
+  const T q2 = q * q;
+  const T q4 = q2 * q2;
+  c.ex = rx * q; c.ey = ry * q; c.ez = Rz * q;
+  const T g = h * q;
+  const T ez2 = c.ez * c.ez;
+  c.f1 = q2;
+  const T f2 = RMB_FMA(T(12.0) * g * c.ez, q2, RMB_FMA(T(-20.0), ez2, T(2.0)) * q4);
+  c.f3 = RMB_FMA(T(-6.0) * g, q2, T(10.0) * c.ez * q4);
+  const T f4 = RMB_FMA(T(-2.0) * g, q2, T(2.0) * c.ez * q4);
+  c.f12 = c.f1 + f2;
+  c.f1ez4 = RMB_FMA(c.f1, c.ez, f4);
+  return c;
+}
+
+// rotation from force: w_i += WF_ij f_j   (units 1/(8 pi eta a^2))
+template <typename T, bool WALL>
+RMB_HD void pair_wf(const PairGeom<T>& p, T fx, T fy, T fz, bool any_near, T r2, T rxy2, T& ux, T& uy, T& uz)
+{
+  const T k = coupling_k(r2, any_near);
+  ux = RMB_FMA(k, RMB_FMA(p.rz, fy, -(p.ry * fz)), ux);
+  uy = RMB_FMA(k, RMB_FMA(p.rx, fz, -(p.rz * fx)), uy);
+  uz = RMB_FMA(k, RMB_FMA(p.ry, fx, -(p.rx * fy)), uz);
+  if (WALL) {
+    const CouplingWall<T> c = coupling_wall(p.rx, p.ry, p.Rz, p.h, rxy2);
+    const T ef = RMB_FMA(c.ez, fz, RMB_FMA(c.ey, fy, c.ex * fx));
+    const T t3 = c.f3 * ef;
+    ux += RMB_FMA(t3, c.ey, RMB_FMA(c.f12 * c.ey, fz, -(c.f1ez4 * fy)));
+    uy += -RMB_FMA(t3, c.ex, RMB_FMA(c.f12 * c.ex, fz, -(c.f1ez4 * fx)));
+    uz = RMB_FMA(c.f1, RMB_FMA(c.ex, fy, -(c.ey * fx)), uz);
+  }
+}
+
+// translation from torque: u_i += UT_ij t_j   (units 1/(8 pi eta a^2));
+// p.h must hold the TARGET height here.
+template <typename T, bool WALL>
+RMB_HD void pair_ut(const PairGeom<T>& p, T tx, T ty, T tz, bool any_near, T r2, T rxy2, T& ux, T& uy, T& uz)
+{
+  const T k = coupling_k(r2, any_near);
+  ux = RMB_FMA(k, RMB_FMA(p.rz, ty, -(p.ry * tz)), ux);
+  uy = RMB_FMA(k, RMB_FMA(p.rx, tz, -(p.rz * tx)), uy);
+  uz = RMB_FMA(k, RMB_FMA(p.ry, tx, -(p.rx * ty)), uz);
+  if (WALL) {
+    const CouplingWall<T> c = coupling_wall(-p.rx, -p.ry, p.Rz, p.h, rxy2);
+    const T cc = RMB_FMA(c.ey, tx, -(c.ex * ty));
+    const T t3 = c.f3 * cc;
+    ux += RMB_FMA(t3, c.ex, RMB_FMA(c.f1ez4, ty, -(c.f1 * c.ey) * tz));
+    uy += RMB_FMA(t3, c.ey, RMB_FMA(c.f1 * c.ex, tz, -(c.f1ez4 * tx)));
+    uz = RMB_FMA(RMB_FMA(c.f3, c.ez, c.f12), cc, uz);
+  }
+}
+
+// Self terms of the couplings (:653-657, :1041-1045): +-h^-4/8 on xy / yx.
+template <typename T>
+RMB_HD void self_wf(T h, T fx, T fy, T& ux, T& uy)
+{
+  const T iz = T(1.0) / h;
+  const T iz2 = iz * iz;
+  const T c = T(0.125) * iz2 * iz2;
+  ux -= c * fy; uy += c * fx;
+}
+template <typename T>
+RMB_HD void self_ut(T h, T tx, T ty, T& ux, T& uy)
+{
+  const T iz = T(1.0) / h;
+  const T iz2 = iz * iz;
+  const T c = T(0.125) * iz2 * iz2;
+  ux += c * ty; uy -= c * tx;
+}
+
+// ------------------------------------------------------------------- WT ----
+// Free space (:1252-1290): far (r >= 2) (-1/2 I + 3/2 rr/r^2)/r^3; near
+// (1 - 27r/32 + 5r^3/64) I + (9/(32r) - 3r/64) rr.  Wall (:1302-1321):
+// fact1 = (1-6ez^2)q^3/2, fact2 = -3q^3/2, fact3 = 3 q^3 ez, fact4 = 3 q^3.
+template <typename T, bool WALL>
+RMB_HD void pair_wt(const PairGeom<T>& p, T tx, T ty, T tz, bool any_near, T r2, T rxy2, T& ux, T& uy, T& uz)
+{
+  const T invr = rsqrt_full(r2);
+  const T invr2 = invr * invr;
+  const T invr3 = invr2 * invr;
+  const T rt = RMB_FMA(p.rz, tz, RMB_FMA(p.ry, ty, p.rx * tx));
+  T A = T(-0.5) * invr3;
+  T B = (T(1.5) * invr2) * invr3 * rt;
+  if (any_near) {
+    const T r = r2 * invr;
+    const T An = RMB_FMA(RMB_FMA(T(0.078125), r2, T(-0.84375)), r, T(1.0));
+    const T Bn = RMB_FMA(T(-0.046875), r, T(0.28125) * invr) * rt;
+    const bool near = lt4(r2);
+    A = near ? An : A;
+    B = near ? Bn : B;
+  }
+  ux = RMB_FMA(A, tx, ux); uy = RMB_FMA(A, ty, uy); uz = RMB_FMA(A, tz, uz);
+  ux = RMB_FMA(B, p.rx, ux); uy = RMB_FMA(B, p.ry, uy); uz = RMB_FMA(B, p.rz, uz);
+  if (WALL) {
+    const T q = rsqrt_full(RMB_FMA(p.Rz, p.Rz, rxy2));
+    const T q3 = q * q * q;
+    const T ex = p.rx * q, ey = p.ry * q, ez = p.Rz * q;
+    const T f1 = RMB_FMA(T(-3.0), ez * ez, T(0.5)) * q3;
+    const T f2 = T(-1.5) * q3;
+    const T f4 = T(3.0) * q3;
+    const T et = RMB_FMA(ez, tz, RMB_FMA(ey, ty, ex * tx));
+    const T cc = RMB_FMA(ex, ty, -(ey * tx));
+    const T f2et = f2 * et;
+    ux += RMB_FMA(f1, tx, RMB_FMA(f2et, ex, -(f4 * ey) * cc));
+    uy += RMB_FMA(f1, ty, RMB_FMA(f2et, ey, (f4 * ex) * cc));
+    uz += RMB_FMA(f1, tz, RMB_FMA(f2, ez, f4 * ez) * et);   // (f2 ez + f3), f3 = f4 ez
+  }
+}
+
+template <typename T, bool WALL>
+RMB_HD void self_wt(T h, T tx, T ty, T tz, T& ux, T& uy, T& uz)
+{
+  T mxx = T(1.0), mzz = T(1.0);
+  if (WALL) {
+    const T iz = T(1.0) / h;
+    const T iz3 = iz * iz * iz;
+    mxx -= T(0.3125) * iz3;
+    mzz -= T(0.125) * iz3;
+  }
+  ux = RMB_FMA(mxx, tx, ux); uy = RMB_FMA(mxx, ty, uy); uz = RMB_FMA(mzz, tz, uz);
+}
+
+}  // namespace rmb

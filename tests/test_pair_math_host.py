@@ -1,0 +1,78 @@
+"""Checks the product's restructured per-pair algebra (csrc/pair_math.cuh +
+mf_core.cuh) on the CPU: the headers are compiled with g++ into a test-only
+harness and compared with the reference's golden outputs.  No GPU needed."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+BLOCKS = {"UF": 0, "UT": 1, "WF": 2, "WT": 3, "UF_UT": 4}
+
+
+@pytest.fixture(scope="module")
+def harness(tmp_path_factory):
+    so = str(tmp_path_factory.mktemp("h") / "host_pair_harness.so")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-DRMB_HOST_ONLY", "-shared", "-fPIC",
+                           os.path.join(HERE, "host_pair_harness.cpp"), "-o", so])
+    lib = ctypes.CDLL(so)
+    dp = ctypes.POINTER(ctypes.c_double)
+    lib.host_mf.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_long, dp, dp, dp,
+                            ctypes.c_double, ctypes.c_double, dp, ctypes.c_int, dp]
+
+    def run(block, wall, r, va, eta, a, L, fp32=False, in_plane=False, vb=None):
+        r = np.ascontiguousarray(r, dtype=np.float64)
+        va = np.ascontiguousarray(va, dtype=np.float64)
+        vb = va if vb is None else np.ascontiguousarray(vb, dtype=np.float64)
+        L = np.ascontiguousarray(L, dtype=np.float64)
+        out = np.empty(r.size)
+        p = lambda x: x.ctypes.data_as(dp)
+        lib.host_mf(BLOCKS[block], int(wall), int(fp32), r.shape[0], p(r), p(va), p(vb), eta, a, p(L), int(in_plane), p(out))
+        return out
+    return run
+
+
+def _cases():
+    g = np.load(os.path.join(HERE, "golden", "mf_golden.npz"))
+    return [str(c) for c in g["cases"]]
+
+
+def relerr(x, ref):
+    return np.linalg.norm(x - ref) / np.linalg.norm(ref)
+
+
+@pytest.mark.parametrize("case", _cases())
+def test_algebra_fp64(golden, harness, case):
+    cloud, lname, wall, blk = case.split("/")
+    r, v = golden[f"{cloud}/r"], golden[f"{cloud}/v"]
+    a, eta = golden[f"{cloud}/a_eta"]
+    L = golden[f"{cloud}/L_{lname}"]
+    out = harness(blk, wall != "no_wall", r, v, eta, a, L, in_plane=(wall == "in_plane"))
+    assert relerr(out, golden[case]) < 1e-12   # BASELINE.json: fp64 parity bar
+
+
+@pytest.mark.parametrize("case", [c for c in _cases() if c.startswith("dilute/") or c.startswith("c1/")])
+def test_algebra_fp32(golden, harness, case):
+    cloud, lname, wall, blk = case.split("/")
+    r, v = golden[f"{cloud}/r"], golden[f"{cloud}/v"]
+    a, eta = golden[f"{cloud}/a_eta"]
+    L = golden[f"{cloud}/L_{lname}"]
+    out = harness(blk, wall != "no_wall", r, v, eta, a, L, fp32=True, in_plane=(wall == "in_plane"))
+    assert relerr(out, golden[case]) < 1e-5    # BASELINE.json: fp32 parity bar
+
+
+@pytest.mark.parametrize("lname", ["open", "xy"])
+@pytest.mark.parametrize("wall", ["single_wall", "no_wall"])
+def test_fused_force_torque(golden, harness, lname, wall):
+    """Fused UF f + UT t (mobility_pycuda.py:1266; no numba twin): oracle = sum of the two golden products."""
+    r, f = golden["dense/r"], golden["dense/v"]
+    a, eta = golden["dense/a_eta"]
+    L = golden[f"dense/L_{lname}"]
+    t = f[::-1].copy()
+    ut = harness("UT", wall != "no_wall", r, t, eta, a, L)
+    ref = golden[f"dense/{lname}/{wall}/UF"] + ut
+    out = harness("UF_UT", wall != "no_wall", r, f, eta, a, L, vb=t)
+    assert relerr(out, ref) < 1e-12
