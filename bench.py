@@ -1,0 +1,265 @@
+#!/usr/bin/env python
+"""bench.py -- single-wall fp64 Mf pair-interactions/s at N = 1M (BASELINE.json config 4).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--n N_BLOBS]
+
+A step = one product u = M f over the whole synthetic blob cloud.  With N > 1
+ranks the targets are sharded by rank, every rank owns the force slice of its
+targets, and a step = NCCL all-gather of the slices + the local product
+(strong scaling: total work N^2 fixed).  One JSON line is printed by rank 0.
+"""
+import argparse
+import ctypes
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FLOP_PER_PAIR = 200.0   # algorithmic flop of one single-wall UF pair as the oracle writes it
+METRIC = "single-wall fp64 Mf pair-interactions/s at N=1M"
+
+
+def make_cloud(n, seed=1234):
+    """10% volume fraction random cloud, all z >= a; a, eta as mobility/test_blobs.py:30-44."""
+    rng = np.random.default_rng(seed)
+    a, eta = 0.13, 7.0
+    side = (n * 4 * np.pi / 3 / 0.1) ** (1.0 / 3.0) * a
+    r = side * rng.random((n, 3))
+    r[:, 2] += a
+    f = rng.standard_normal((n, 3))
+    return r, f, a, eta
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
+                 "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                 "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                 "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if mask & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def cpu_reference_rate(r, f, a, eta, budget_s=12.0):
+    """The oracle (C/OpenMP port of mobility_numba) on a bounded sample: the first m targets against ALL sources."""
+    import oracle
+    n = r.shape[0]
+    m = min(n, 64)
+    t0 = time.perf_counter()
+    oracle.mobility_product("UF", "single_wall", r, f, eta, a, targets=(0, m))
+    dt = time.perf_counter() - t0
+    rate = m * n / dt
+    m2 = int(min(n, max(m, budget_s * rate / n)))
+    t0 = time.perf_counter()
+    oracle.mobility_product("UF", "single_wall", r, f, eta, a, targets=(0, m2))
+    dt = time.perf_counter() - t0
+    return m2 * n / dt, oracle.threads(), "targets [0,%d) x all %d sources, %.1f s" % (m2, n, dt)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    r, f, a, eta = make_cloud(args.n)
+    times, sample, cores = [], "", 0
+    for it in range(args.warmup + args.steps):
+        rate, cores, sample = cpu_reference_rate(r, f, a, eta, budget_s=args.ref_budget)
+        if it >= args.warmup:
+            times.append(rate)
+    v = float(np.mean(times))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "pairs/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * args.n * args.n / v,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "C4: single-wall UF, N=%d random blobs, 10%% volume fraction, open boundaries" % args.n,
+                   "note": "CPU port of mobility_numba (oracle/, C+OpenMP); ms_per_step extrapolated from the sample"},
+        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from rigidmultiblobswall_b200 import _lib, mobility as mb
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    n = args.n
+    r_np, f_np, a, eta = make_cloud(n)
+    # contiguous target ranges, one per rank
+    cuts = [(n * k) // world for k in range(world + 1)]
+    off, cnt = cuts[rank], cuts[rank + 1] - cuts[rank]
+    equal = all(cuts[k + 1] - cuts[k] == cnt for k in range(world))
+
+    r_d = torch.from_numpy(r_np).to(dev).reshape(-1)
+    f_full = torch.from_numpy(f_np).to(dev).reshape(-1)
+    f_loc = f_full[3 * off:3 * (off + cnt)].clone()
+    u_loc = torch.empty(3 * cnt, dtype=torch.float64, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def gather_forces():
+        if world == 1:
+            return f_loc
+        if equal:
+            dist.all_gather_into_tensor(f_full, f_loc)
+        else:
+            parts = [f_full[3 * cuts[k]:3 * cuts[k + 1]] for k in range(world)]
+            dist.all_gather(parts, f_loc)
+        return f_full
+
+    def step():
+        flush.zero_()                       # L2 flush between iterations (inside the timed region; ~0.1 ms)
+        fv = gather_forces()
+        mb.mobility_product(mb.UF, mb.SINGLE_WALL, r_d, fv, eta, a, targets=(off, cnt), out=u_loc)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    # FP64 FMA-pipe peak of this GPU, measured now (MEASURED_PEAKS.json has no FP64 figure)
+    peak_flops, _ = _lib.fma_peak(_lib.FP64, 100000)
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms = timed(step, args.steps)
+    clocks = sampler.stop()
+    pairs_per_step = float(n) * float(n)
+    value = pairs_per_step * args.steps / (ms * 1e-3)
+
+    # parity spot check in the same run: 48 rows of this rank's shard against the oracle
+    parity = None
+    if rank == 0 and not args.no_parity:
+        import oracle
+        b = off + min(cnt - 48, 1234) if cnt > 48 else off
+        e = min(b + 48, off + cnt)
+        ref = oracle.mobility_product("UF", "single_wall", r_np, f_np, eta, a, targets=(b, e))
+        got = u_loc[3 * (b - off):3 * (e - off)].cpu().numpy()
+        parity = float(np.linalg.norm(got - ref) / np.linalg.norm(ref))
+
+    # end to end through the public NumPy API: host buffers in, host result out, every step
+    r_host = torch.from_numpy(r_np).pin_memory().numpy()
+    f_host = torch.from_numpy(f_np).pin_memory().numpy()
+
+    def e2e_step():
+        u = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r_host, f_host, eta, a, targets=(off, cnt))
+        return u
+
+    e2e_step()
+    ms_e2e = timed(e2e_step, args.steps)
+    e2e_value = pairs_per_step * args.steps / (ms_e2e * 1e-3)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        v, cores, sample = cpu_reference_rate(r_np, f_np, a, eta, budget_s=args.ref_budget)
+        cpu = {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port", "sample": sample}
+
+    if rank == 0:
+        # dominant kernel = mf_kernel<double,UF,wall,open,TMA>; one launch per step per rank; the
+        # step's other launches (L2 flush memset, prepare_kernel) are < 0.1% of it
+        launch_ms = ms / args.steps
+        achieved = (float(cnt) * n * FLOP_PER_PAIR) / (launch_ms * 1e-3) / 1e12
+        plan_launches = 2   # prepare_kernel + mf_kernel (n_split == 1 at this size: no finish_kernel)
+        line = {
+            "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C4: single-wall UF, N=%d random blobs, 10%% volume fraction, open boundaries" % n,
+                       "sharding": "targets by rank, sources replicated, NCCL all-gather of force slices per step"
+                       if world > 1 else "single GPU",
+                       "l2": "flushed between iterations (256 MiB memset inside the timed region)"},
+            "roofline": {"bound": "fp64_fma", "achieved": achieved, "peak": peak_flops / 1e12, "unit": "TFLOP/s",
+                         "frac": achieved / (peak_flops / 1e12), "traffic": None,
+                         "flop_per_pair": FLOP_PER_PAIR,
+                         "peak_source": "rmb_fma_peak (FP64 FMA probe, measured in this run on this GPU)"},
+            "cpu_baseline": cpu,
+            "e2e": {"value": e2e_value, "unit": "pairs/s", "ms_per_step": ms_e2e / args.steps,
+                    "h2d_bytes_per_step": int(world * 2 * 24 * n), "d2h_bytes_per_step": int(24 * n)},
+            "gpu_launches": int(args.steps * plan_launches * world),
+            "clocks": clocks,
+            "parity_rel_err_vs_oracle": parity,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--n", type=int, default=1000000)
+    ap.add_argument("--ref-budget", type=float, default=8.0, help="seconds of CPU work per reference sample")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-parity", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,110 @@
+/*
+ * rmb_mobility.h -- C ABI of the B200 blob-mobility product (librmb_mobility.so).
+ *
+ * Drop-in boundary: the module-level functions of the reference's
+ * mobility/mobility.py,
+ *     f(r_vectors, vec, eta, a, *args, periodic_length=L) -> flat 3N array
+ * (mobility.py:222-548 PyCUDA wrappers, :1119-1341 numba wrappers).  Where the
+ * reference's PyCUDA path binds one __global__ kernel per block
+ * (mobility_pycuda.py:2235-2746), a maintainer binds ONE entry point,
+ * rmb_mobility_product(), selected by (block, wall).  See INTEGRATION.md for
+ * the ctypes stub.
+ *
+ * Conventions
+ *  - every pointer marked "device" is a CUDA device pointer (e.g. a PyTorch
+ *    tensor's data_ptr()); "host" pointers are ordinary host memory;
+ *  - all device arrays are float64, C-contiguous, interleaved xyz, exactly the
+ *    reference's layout; `precision` selects only the
+ *    arithmetic of the O(N^2) pair kernel;
+ *  - calls enqueue work on `stream` (a cudaStream_t, NULL = default stream)
+ *    and never synchronise; inputs are not modified;
+ *  - the return value is 0 on success, otherwise a negative RMB_E_* code or a
+ *    positive cudaError_t; rmb_last_error() describes the last failure of the
+ *    calling thread.  Like the reference, bad geometry (coincident blobs) is
+ *    not an error: it shows up as NaN/Inf in the output.
+ */
+#ifndef RMB_MOBILITY_H
+#define RMB_MOBILITY_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RMB_VERSION 100 /* 0.1.0 */
+
+/* block: which mobility block is applied (mobility.py naming in comments) */
+#define RMB_UF 0    /* *_mobility_trans_times_force        (mobility.py:222,288,1119,1132) */
+#define RMB_UT 1    /* *_mobility_trans_times_torque       (:427,482,1200,1213)            */
+#define RMB_WF 2    /* *_mobility_rot_times_force          (:300,328,1258,1273)            */
+#define RMB_WT 3    /* *_mobility_rot_times_torque         (:342,370,1301,1316)            */
+#define RMB_UF_UT 4 /* *_mobility_trans_times_force_torque (:384,413), vec_b = torque      */
+
+/* wall */
+#define RMB_NO_WALL 0     /* no_wall_* : unbounded RPY                                   */
+#define RMB_SINGLE_WALL 1 /* single_wall_* : Swan-Brady wall, heights clamped to z >= a,
+                             damping B applied on both sides (mobility.py:52-84)          */
+
+/* precision of the pair arithmetic */
+#define RMB_FP64 0
+#define RMB_FP32 1
+
+/* flags */
+#define RMB_IN_PLANE 1    /* in_plane_* (mobility.py:255,454,1166,1235): z column and row zero */
+#define RMB_NO_TMA 2      /* stage source tiles with plain loads instead of cp.async.bulk (debug) */
+
+/* error codes */
+#define RMB_E_ARG (-1)        /* invalid argument                          */
+#define RMB_E_WORKSPACE (-2)  /* workspace too small                       */
+#define RMB_E_NODEVICE (-3)   /* no CUDA device / wrong architecture       */
+
+int rmb_version(void);
+const char *rmb_last_error(void);
+
+/* Number of SMs of the current device (>0), or a negative RMB_E_* code. */
+int rmb_device_sm_count(void);
+
+/*
+ * Bytes of device scratch rmb_mobility_product() needs for this problem
+ * (packed source records + damping factors + per-split partial sums).
+ * L is a host pointer to 3 doubles (NULL = not periodic).
+ */
+size_t rmb_workspace_bytes(int block, int precision, long n_targets, long n_sources, const double *L);
+
+/*
+ * out[0:3*n_targets] = rows [target_offset, target_offset + n_targets) of
+ *     B * M(r_eff) * (B * vec)            (single wall)
+ *     M(r) * vec                          (no wall)
+ * where M is the (block, wall) blob mobility over ALL n_sources blobs and the
+ * pair sum runs over the 3^d nearest image boxes of the d periodic directions
+ * (mobility_numba.py:166-197).  n_targets = n_sources, target_offset = 0 is
+ * the reference's call; a rank that owns a shard of the targets passes its
+ * range, and the self term stays correct because it is matched on the global
+ * index.
+ *
+ *   r_sources   device, 3*n_sources   blob positions (unclamped)
+ *   vec_a       device, 3*n_sources   force (UF, WF, UF_UT) or torque (UT, WT)
+ *   vec_b       device, 3*n_sources   torque for RMB_UF_UT, else NULL
+ *   L           host, 3 doubles or NULL; component <= 0: not periodic
+ *   out         device, 3*n_targets
+ *   workspace   device, >= rmb_workspace_bytes(...) bytes, 16-byte aligned
+ */
+int rmb_mobility_product(int block, int wall, int precision, int flags,
+                         long n_targets, long n_sources, long target_offset,
+                         const double *r_sources, const double *vec_a, const double *vec_b,
+                         double eta, double a, const double *L,
+                         double *out, void *workspace, size_t workspace_bytes, void *stream);
+
+/*
+ * FP64 (precision = RMB_FP64) or FP32 FMA-pipe peak probe: runs `iters`
+ * dependent-chain-free FMAs per thread on a full grid and returns the
+ * measured rate in FLOP/s through *flops (host).  Synchronises.  Used by
+ * bench.py for the roofline denominator (MEASURED_PEAKS.json has no FP64 figure).
+ */
+int rmb_fma_peak(int precision, int iters, double *flops, double *elapsed_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RMB_MOBILITY_H */

@@ -18,10 +18,27 @@ BLOCKS = {"UF": 0, "UT": 1, "WF": 2, "WT": 3}
 _lib = None
 
 
+def _cpu_signature():
+    """-march=native code must not travel between machines: rebuild when the host CPU changes."""
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("flags"):
+                    return str(hash(line.strip()))
+    except OSError:
+        pass
+    return "unknown"
+
+
 def build(force=False):
     src = os.path.join(_HERE, "mobility_oracle.c")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+    sig_file = _SO + ".cpu"
+    sig = _cpu_signature()
+    old = open(sig_file).read() if os.path.exists(sig_file) else ""
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src) or old != sig:
         subprocess.check_call(["make", "-C", _HERE, "-s", "-B"])
+        with open(sig_file, "w") as f:
+            f.write(sig)
     return _SO
 
 

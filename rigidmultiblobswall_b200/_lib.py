@@ -1,0 +1,57 @@
+"""ctypes binding of librmb_mobility.so (C ABI: include/rmb_mobility.h).
+
+There is no CPU fallback: if the library is missing and cannot be built, or no
+CUDA device is present, calls raise."""
+import ctypes
+import os
+
+from . import _build
+
+UF, UT, WF, WT, UF_UT = 0, 1, 2, 3, 4
+NO_WALL, SINGLE_WALL = 0, 1
+FP64, FP32 = 0, 1
+IN_PLANE, NO_TMA = 1, 2
+
+_lib = None
+
+
+class RmbError(RuntimeError):
+    pass
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_build.SO):
+        _build.build()
+    lib = ctypes.CDLL(_build.SO)
+    c_dp = ctypes.c_void_p
+    lib.rmb_version.restype = ctypes.c_int
+    lib.rmb_last_error.restype = ctypes.c_char_p
+    lib.rmb_device_sm_count.restype = ctypes.c_int
+    lib.rmb_workspace_bytes.restype = ctypes.c_size_t
+    lib.rmb_workspace_bytes.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_long, ctypes.c_long,
+                                        ctypes.POINTER(ctypes.c_double)]
+    lib.rmb_mobility_product.restype = ctypes.c_int
+    lib.rmb_mobility_product.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                         ctypes.c_long, ctypes.c_long, ctypes.c_long,
+                                         c_dp, c_dp, c_dp, ctypes.c_double, ctypes.c_double,
+                                         ctypes.POINTER(ctypes.c_double), c_dp, c_dp, ctypes.c_size_t, c_dp]
+    lib.rmb_fma_peak.restype = ctypes.c_int
+    lib.rmb_fma_peak.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double),
+                                 ctypes.POINTER(ctypes.c_double)]
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc != 0:
+        raise RmbError("librmb_mobility: error %d: %s" % (rc, load().rmb_last_error().decode()))
+
+
+def fma_peak(precision=FP64, iters=200000):
+    """Measured FMA-pipe peak in FLOP/s (roofline denominator), elapsed ms."""
+    fl, ms = ctypes.c_double(), ctypes.c_double()
+    check(load().rmb_fma_peak(precision, iters, ctypes.byref(fl), ctypes.byref(ms)))
+    return fl.value, ms.value

@@ -10,14 +10,23 @@ enum Block { UF = 0, UT = 1, WF = 2, WT = 3, UF_UT = 4 };
 
 // One packed source blob in HBM / shared memory: position followed by NV
 // 3-vectors (NV = 1: force or torque; NV = 2: force and torque/a for the
-// fused UF+UT product).  48 B (fp64, NV=1) = three 16-byte shared-memory
-// broadcasts per pair.  Positions are in units of a for the open-boundary
-// kernels and unscaled for the pseudo-periodic ones (the wrap is done in the
-// caller's length unit, exactly where the reference does it).
+// fused UF+UT product), padded to a multiple of 16 bytes so that a record is
+// read with 16-byte shared-memory broadcasts only:
+//   fp64 NV=1: 6 words = 48 B (3 x LDS.128)   fp64 NV=2: 10 words = 80 B
+//   fp32 NV=1: 8 words = 32 B (2 x LDS.128)   fp32 NV=2: 12 words = 48 B
+// Positions are in units of a for the open-boundary kernels and unscaled for
+// the pseudo-periodic ones (the wrap is done in the caller's length unit,
+// exactly where the reference does it).
+template <typename T, int NV> struct RecWords;
+template <> struct RecWords<double, 1> { static constexpr int value = 6; };
+template <> struct RecWords<double, 2> { static constexpr int value = 10; };
+template <> struct RecWords<float, 1> { static constexpr int value = 8; };
+template <> struct RecWords<float, 2> { static constexpr int value = 12; };
+
 template <typename T, int NV>
-struct alignas(8) SrcRec {
+struct alignas(16) SrcRec {
   T x, y, z;
-  T v[3 * NV];
+  T v[RecWords<T, NV>::value - 3];
 };
 
 // Pseudo-periodic parameters (host-filled).  L[d] <= 0: not periodic in d.

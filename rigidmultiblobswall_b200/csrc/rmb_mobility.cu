@@ -1,0 +1,512 @@
+// rmb_mobility.cu -- B200 (sm_100a) blob-mobility product Mf and its C ABI.
+//
+// Replaces the per-block PyCUDA kernels of the reference
+// (/root/reference/mobility/mobility_pycuda.py:150-2081, host wrappers
+// :2235-2746) with one templated N-body tile kernel:
+//   prepare_kernel : O(N) -- height clamp, damping B, 1/a scaling, packing of
+//                    position+vector into 16-byte aligned source records
+//   mf_kernel      : O(N^2 n_boxes) -- one thread per target, source tiles
+//                    streamed through shared memory by bulk async copies
+//                    (cp.async.bulk + mbarrier, 2 stages); FP64 or FP32
+//   finish_kernel  : O(N n_split) -- sum of source-split partials, self term,
+//                    normalisation, damping B, in-plane mask
+// See DESIGN.md for the layout and the roofline.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/rmb_mobility.h"
+#include "mf_core.cuh"
+
+using namespace rmb;
+
+namespace {
+
+constexpr int TPB = 128;    // targets (threads) per CTA
+constexpr int TILE = 256;   // sources per shared-memory tile
+constexpr int STAGES = 2;
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* msg)
+{
+  snprintf(g_err, sizeof(g_err), "%s", msg);
+  return code;
+}
+int fail_cuda(cudaError_t e, const char* where)
+{
+  snprintf(g_err, sizeof(g_err), "%s: %s", where, cudaGetErrorString(e));
+  return (int)e;
+}
+
+// ------------------------------------------------------------ PTX helpers --
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+// 1-D bulk async copy global -> shared (TMA engine, SASS UBLKCP), completion
+// counted in bytes on an mbarrier.  dst/src 16-byte aligned, bytes % 16 == 0.
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init()
+{
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+
+// 16-byte shared-memory loads of one record (all lanes read the same address:
+// a broadcast, one wavefront each).
+template <int W>
+__device__ __forceinline__ void load_rec(const double* p, double (&w)[W])
+{
+#pragma unroll
+  for (int k = 0; k < W / 2; k++) {
+    const double2 v = reinterpret_cast<const double2*>(p)[k];
+    w[2 * k] = v.x; w[2 * k + 1] = v.y;
+  }
+}
+template <int W>
+__device__ __forceinline__ void load_rec(const float* p, float (&w)[W])
+{
+#pragma unroll
+  for (int k = 0; k < W / 4; k++) {
+    const float4 v = reinterpret_cast<const float4*>(p)[k];
+    w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
+  }
+}
+
+// ---------------------------------------------------------------- prepare --
+// mobility.py:52-84 fused on the device: r_eff (z <- a where z <= a), B_ii
+// (z/a where z < a), B*vec; plus 1/a scaling (open-boundary kernels), the
+// in-plane mask and the 1/a factor of the fused torque.  Records past n are
+// zero so a full tile can always be copied.
+template <typename T, int NV>
+__global__ void prepare_kernel(long n, long n_pad, const double* __restrict__ r, const double* __restrict__ va,
+                               const double* __restrict__ vb, double a, int wall, int scaled, int in_plane,
+                               SrcRec<T, NV>* __restrict__ rec, double* __restrict__ damp)
+{
+  const long j = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n_pad) return;
+  SrcRec<T, NV> o;
+  constexpr int W = RecWords<T, NV>::value;
+  T* w = reinterpret_cast<T*>(&o);
+#pragma unroll
+  for (int k = 0; k < W; k++) w[k] = T(0);
+  if (j < n) {
+    const double inva = 1.0 / a;
+    const double s = scaled ? inva : 1.0;
+    double z = r[3 * j + 2], B = 1.0;
+    if (wall) {
+      B = (z < a) ? z / a : 1.0;
+      z = (z <= a) ? a : z;
+    }
+    damp[j] = B;
+    o.x = T(r[3 * j] * s); o.y = T(r[3 * j + 1] * s); o.z = T(z * s);
+#pragma unroll
+    for (int c = 0; c < 3; c++) o.v[c] = T(B * va[3 * j + c]);
+    if (NV == 2) {
+#pragma unroll
+      for (int c = 0; c < 3; c++) o.v[3 + c] = T(B * vb[3 * j + c] * inva);
+    }
+    if (in_plane) {
+      o.v[2] = T(0);
+      if (NV == 2) o.v[5] = T(0);
+    }
+  }
+  rec[j] = o;
+}
+
+// ------------------------------------------------------------ main kernel --
+template <typename T, int NV>
+struct MfArgs {
+  const SrcRec<T, NV>* src;  // n_tiles * TILE records (zero padded)
+  long n_src, n_tgt, tgt_off;
+  Periodic<T> P;
+  T inva;
+  int n_tiles;       // ceil(n_src / TILE)
+  int n_vt;          // virtual tiles = n_boxes * n_tiles
+  int vt_per_split;  // virtual tiles handled by one blockIdx.y
+  int n_split;
+  T* partial;        // [n_split][n_tgt][3] when n_split > 1
+  double* out;       // [n_tgt][3], written here when n_split == 1
+  const double* damp;
+  double norm;
+  int in_plane;
+};
+
+// Pairs of one target with the `cnt` sources of one shared-memory tile.
+// DIAG: the tile may contain the target itself (central box only): that lane
+// gets a finite dummy geometry and a zero vector; the closed-form self term
+// is added once per target in the epilogue.
+template <typename T, int BLOCK, bool WALL, bool PERIODIC, bool DIAG>
+__device__ __forceinline__ void tile_pairs(const T* __restrict__ tile, int cnt, long j0, long gi, const Target<T>& t,
+                                           const Periodic<T>& P, T sx, T sy, T sz, T inva, T& ux, T& uy, T& uz)
+{
+  constexpr int NV = (BLOCK == UF_UT) ? 2 : 1;
+  constexpr int W = RecWords<T, NV>::value;
+#pragma unroll 2
+  for (int j = 0; j < cnt; j++) {
+    T w[W];
+    load_rec<W>(tile + j * W, w);
+    PairGeom<T> g;
+    T r2, rxy2;
+    pair_geometry<T, WALL, PERIODIC>(t, w[0], w[1], w[2], P, sx, sy, sz, inva, g, r2, rxy2);
+    if (DIAG) {
+      const bool self = (j0 + j == gi);
+      if (self) { r2 = T(1); rxy2 = T(1); }
+#pragma unroll
+      for (int c = 3; c < 3 + 3 * NV; c++) w[c] = self ? T(0) : w[c];
+    }
+    const bool any_near = __any_sync(0xffffffffu, lt4(r2));
+    pair_apply<T, BLOCK, WALL>(g, t.h, w + 3, any_near, r2, rxy2, ux, uy, uz);
+  }
+}
+
+template <typename T, int BLOCK, bool WALL, bool PERIODIC, bool TMA>
+__global__ void __launch_bounds__(TPB) mf_kernel(const __grid_constant__ MfArgs<T, (BLOCK == UF_UT) ? 2 : 1> A)
+{
+  constexpr int NV = (BLOCK == UF_UT) ? 2 : 1;
+  constexpr int W = RecWords<T, NV>::value;
+  constexpr uint32_t TILE_BYTES = TILE * W * sizeof(T);
+  __shared__ alignas(128) T tile[TMA ? STAGES : 1][TILE * W];
+  __shared__ alignas(8) uint64_t full[STAGES];
+
+  const int tid = threadIdx.x;
+  const long li = (long)blockIdx.x * TPB + tid;
+  const bool valid = li < A.n_tgt;
+  const long gi = A.tgt_off + (valid ? li : A.n_tgt - 1);
+  const long blk_g0 = A.tgt_off + (long)blockIdx.x * TPB, blk_g1 = blk_g0 + TPB;
+
+  Target<T> t;
+  {
+    const SrcRec<T, NV>& me = A.src[gi];
+    t.x = me.x; t.y = me.y; t.z = me.z;
+    t.h = PERIODIC ? me.z * A.inva : me.z;
+  }
+  const int v0 = blockIdx.y * A.vt_per_split;
+  const int v1 = min(v0 + A.vt_per_split, A.n_vt);
+  const T* srcw = reinterpret_cast<const T*>(A.src);
+
+  if (TMA) {
+    if (tid == 0) {
+#pragma unroll
+      for (int s = 0; s < STAGES; s++) mbar_init(&full[s], 1);
+      fence_barrier_init();
+    }
+    __syncthreads();
+    if (tid == 0 && v0 < v1) {
+      mbar_expect_tx(&full[0], TILE_BYTES);
+      bulk_g2s(tile[0], srcw + (size_t)(v0 % A.n_tiles) * TILE * W, TILE_BYTES, &full[0]);
+    }
+  }
+
+  T ux = 0, uy = 0, uz = 0;
+  int stage = 0;
+  uint32_t phases = 0;
+  for (int v = v0; v < v1; v++) {
+    const int box = v / A.n_tiles;
+    const int tl = v - box * A.n_tiles;
+    if (TMA) {
+      // stage^1 was last read in iteration v-1, which ended with __syncthreads
+      if (tid == 0 && v + 1 < v1) {
+        mbar_expect_tx(&full[stage ^ 1], TILE_BYTES);
+        bulk_g2s(tile[stage ^ 1], srcw + (size_t)((v + 1) % A.n_tiles) * TILE * W, TILE_BYTES, &full[stage ^ 1]);
+      }
+      mbar_wait(&full[stage], (phases >> stage) & 1u);
+      phases ^= (1u << stage);
+    } else {
+      const T* gsrc = srcw + (size_t)tl * TILE * W;
+      for (int k = tid; k < TILE * W; k += TPB) tile[0][k] = gsrc[k];
+      __syncthreads();
+    }
+    T sx = 0, sy = 0, sz = 0;
+    bool central = true;
+    if (PERIODIC) box_shift(A.P, box, sx, sy, sz, central);
+    const long j0 = (long)tl * TILE;
+    const int cnt = (int)min((long)TILE, A.n_src - j0);
+    const bool diag = central && (j0 < blk_g1) && (j0 + cnt > blk_g0);
+    const T* tp = tile[TMA ? stage : 0];
+    if (diag) tile_pairs<T, BLOCK, WALL, PERIODIC, true>(tp, cnt, j0, gi, t, A.P, sx, sy, sz, A.inva, ux, uy, uz);
+    else tile_pairs<T, BLOCK, WALL, PERIODIC, false>(tp, cnt, j0, gi, t, A.P, sx, sy, sz, A.inva, ux, uy, uz);
+    __syncthreads();
+    if (TMA) stage ^= 1;
+  }
+
+  if (!valid) return;
+  if (A.n_split == 1) {
+    // epilogue fused: self term, normalisation, damping
+    const SrcRec<T, NV>& me = A.src[gi];
+    double sv[3 * NV];
+#pragma unroll
+    for (int c = 0; c < 3 * NV; c++) sv[c] = (double)me.v[c];
+    double dx = (double)ux, dy = (double)uy, dz = (double)uz;
+    self_apply<double, BLOCK, WALL>((double)t.h, sv, dx, dy, dz);
+    const double sc = A.norm * A.damp[gi];
+    A.out[3 * li] = dx * sc;
+    A.out[3 * li + 1] = dy * sc;
+    A.out[3 * li + 2] = A.in_plane ? 0.0 : dz * sc;
+  } else {
+    T* p = A.partial + ((size_t)blockIdx.y * A.n_tgt + li) * 3;
+    p[0] = ux; p[1] = uy; p[2] = uz;
+  }
+}
+
+// Sum of the source-split partials + self term + normalisation + damping.
+template <typename T, int BLOCK, bool WALL, bool PERIODIC>
+__global__ void finish_kernel(const MfArgs<T, (BLOCK == UF_UT) ? 2 : 1> A)
+{
+  constexpr int NV = (BLOCK == UF_UT) ? 2 : 1;
+  const long li = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (li >= A.n_tgt) return;
+  const long gi = A.tgt_off + li;
+  double dx = 0, dy = 0, dz = 0;
+  for (int s = 0; s < A.n_split; s++) {
+    const T* p = A.partial + ((size_t)s * A.n_tgt + li) * 3;
+    dx += (double)p[0]; dy += (double)p[1]; dz += (double)p[2];
+  }
+  const SrcRec<T, NV>& me = A.src[gi];
+  double sv[3 * NV];
+#pragma unroll
+  for (int c = 0; c < 3 * NV; c++) sv[c] = (double)me.v[c];
+  const double h = PERIODIC ? (double)me.z * (double)A.inva : (double)me.z;
+  self_apply<double, BLOCK, WALL>(h, sv, dx, dy, dz);
+  const double sc = A.norm * A.damp[gi];
+  A.out[3 * li] = dx * sc;
+  A.out[3 * li + 1] = dy * sc;
+  A.out[3 * li + 2] = A.in_plane ? 0.0 : dz * sc;
+}
+
+// ---------------------------------------------------------- host dispatch --
+int g_sm_count = 0;
+
+int sm_count()
+{
+  if (g_sm_count > 0) return g_sm_count;
+  int dev = 0, n = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return fail(RMB_E_NODEVICE, "no CUDA device");
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+    return fail(RMB_E_NODEVICE, "cannot query the SM count");
+  g_sm_count = n;
+  return n;
+}
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct Plan {
+  int n_tiles, n_boxes, n_vt, n_split, vt_per_split, tgt_blocks;
+  size_t rec_bytes, off_damp, off_partial, total;
+};
+
+// One place decides the decomposition; rmb_workspace_bytes and the launch
+// must agree.  Source splitting (blockIdx.y) is only used when the target
+// blocks alone cannot fill the chip (8 CTAs of 128 threads per SM).
+int make_plan(int block, int precision, long n_tgt, long n_src, const double* L, Plan& p)
+{
+  const int sms = sm_count();
+  if (sms <= 0) return sms;
+  const int nv = (block == RMB_UF_UT) ? 2 : 1;
+  const size_t word = precision == RMB_FP32 ? 4 : 8;
+  const int W = precision == RMB_FP32 ? (nv == 2 ? 12 : 8) : (nv == 2 ? 10 : 6);
+  p.n_tiles = (int)((n_src + TILE - 1) / TILE);
+  p.n_boxes = 1;
+  if (L) for (int d = 0; d < 3; d++) if (L[d] > 0) p.n_boxes *= 3;
+  p.n_vt = p.n_tiles * p.n_boxes;
+  p.tgt_blocks = (int)((n_tgt + TPB - 1) / TPB);
+  const int want = sms * 8;
+  int split = (want + p.tgt_blocks - 1) / p.tgt_blocks;
+  if (split > p.n_vt) split = p.n_vt;
+  if (split < 1) split = 1;
+  p.vt_per_split = (p.n_vt + split - 1) / split;
+  p.n_split = (p.n_vt + p.vt_per_split - 1) / p.vt_per_split;
+  p.rec_bytes = (size_t)p.n_tiles * TILE * W * word;
+  p.off_damp = align_up(p.rec_bytes, 256);
+  p.off_partial = align_up(p.off_damp + (size_t)n_src * sizeof(double), 256);
+  p.total = p.off_partial + (p.n_split > 1 ? (size_t)p.n_split * n_tgt * 3 * word : 0);
+  return 0;
+}
+
+struct Call {
+  int block, wall, precision, flags;
+  long n_tgt, n_src, tgt_off;
+  const double *r, *va, *vb;
+  double eta, a;
+  double L[3];
+  double* out;
+  char* ws;
+  cudaStream_t stream;
+  Plan plan;
+};
+
+template <typename T, int BLOCK, bool WALL, bool PERIODIC>
+int launch(const Call& c)
+{
+  constexpr int NV = (BLOCK == UF_UT) ? 2 : 1;
+  const Plan& p = c.plan;
+  SrcRec<T, NV>* rec = reinterpret_cast<SrcRec<T, NV>*>(c.ws);
+  double* damp = reinterpret_cast<double*>(c.ws + p.off_damp);
+  const long n_pad = (long)p.n_tiles * TILE;
+  const int in_plane = (c.flags & RMB_IN_PLANE) ? 1 : 0;
+  prepare_kernel<T, NV><<<(unsigned)((n_pad + 255) / 256), 256, 0, c.stream>>>(
+      c.n_src, n_pad, c.r, c.va, c.vb, c.a, WALL ? 1 : 0, PERIODIC ? 0 : 1, in_plane, rec, damp);
+
+  MfArgs<T, NV> A;
+  A.src = rec;
+  A.n_src = c.n_src; A.n_tgt = c.n_tgt; A.tgt_off = c.tgt_off;
+  A.P.nbox = p.n_boxes;
+  for (int d = 0; d < 3; d++) {
+    A.P.per[d] = PERIODIC && c.L[d] > 0;
+    A.P.L[d] = T(c.L[d]);
+    A.P.invL[d] = A.P.per[d] ? T(1.0 / c.L[d]) : T(0);
+  }
+  A.inva = T(1.0 / c.a);
+  A.n_tiles = p.n_tiles; A.n_vt = p.n_vt; A.vt_per_split = p.vt_per_split; A.n_split = p.n_split;
+  A.partial = reinterpret_cast<T*>(c.ws + p.off_partial);
+  A.out = c.out;
+  A.damp = damp;
+  A.norm = block_norm(BLOCK, c.eta, c.a);
+  A.in_plane = in_plane;
+
+  const dim3 grid((unsigned)p.tgt_blocks, (unsigned)p.n_split);
+  if (c.flags & RMB_NO_TMA) mf_kernel<T, BLOCK, WALL, PERIODIC, false><<<grid, TPB, 0, c.stream>>>(A);
+  else mf_kernel<T, BLOCK, WALL, PERIODIC, true><<<grid, TPB, 0, c.stream>>>(A);
+  if (p.n_split > 1)
+    finish_kernel<T, BLOCK, WALL, PERIODIC><<<(unsigned)((c.n_tgt + 127) / 128), 128, 0, c.stream>>>(A);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail_cuda(e, "rmb_mobility_product launch");
+  return 0;
+}
+
+template <typename T, int BLOCK>
+int launch_wp(const Call& c, bool per)
+{
+  if (c.wall == RMB_SINGLE_WALL) return per ? launch<T, BLOCK, true, true>(c) : launch<T, BLOCK, true, false>(c);
+  return per ? launch<T, BLOCK, false, true>(c) : launch<T, BLOCK, false, false>(c);
+}
+
+template <typename T>
+int launch_block(const Call& c, bool per)
+{
+  switch (c.block) {
+    case RMB_UF: return launch_wp<T, UF>(c, per);
+    case RMB_UT: return launch_wp<T, UT>(c, per);
+    case RMB_WF: return launch_wp<T, WF>(c, per);
+    case RMB_WT: return launch_wp<T, WT>(c, per);
+    case RMB_UF_UT: return launch_wp<T, UF_UT>(c, per);
+  }
+  return fail(RMB_E_ARG, "unknown block");
+}
+
+// ------------------------------------------------------------ FMA probe ----
+template <typename T>
+__global__ void fma_peak_kernel(int iters, T* sink)
+{
+  T a0 = T(threadIdx.x) * T(1e-3), a1 = a0 + T(1), a2 = a0 + T(2), a3 = a0 + T(3);
+  T a4 = a0 + T(4), a5 = a0 + T(5), a6 = a0 + T(6), a7 = a0 + T(7);
+  const T m = T(0.999999), c = T(1e-7);
+  for (int i = 0; i < iters; i++) {
+    a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+    a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+  }
+  const T s = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+  if (s == T(-1)) sink[0] = s;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ C ABI --
+extern "C" {
+
+int rmb_version(void) { return RMB_VERSION; }
+const char* rmb_last_error(void) { return g_err; }
+int rmb_device_sm_count(void) { return sm_count(); }
+
+size_t rmb_workspace_bytes(int block, int precision, long n_targets, long n_sources, const double* L)
+{
+  Plan p;
+  if (block < 0 || block > RMB_UF_UT || n_targets < 0 || n_sources < 0) return 0;
+  if (make_plan(block, precision, n_targets, n_sources, L, p) != 0) return 0;
+  return p.total;
+}
+
+int rmb_mobility_product(int block, int wall, int precision, int flags, long n_targets, long n_sources,
+                         long target_offset, const double* r_sources, const double* vec_a, const double* vec_b,
+                         double eta, double a, const double* L, double* out, void* workspace,
+                         size_t workspace_bytes, void* stream)
+{
+  if (block < 0 || block > RMB_UF_UT) return fail(RMB_E_ARG, "block must be RMB_UF..RMB_UF_UT");
+  if (wall != RMB_NO_WALL && wall != RMB_SINGLE_WALL) return fail(RMB_E_ARG, "wall must be 0 or 1");
+  if (precision != RMB_FP64 && precision != RMB_FP32) return fail(RMB_E_ARG, "precision must be 0 or 1");
+  if (n_targets < 0 || n_sources < 0 || target_offset < 0 || target_offset + n_targets > n_sources)
+    return fail(RMB_E_ARG, "target range must lie inside [0, n_sources)");
+  if (n_targets == 0 || n_sources == 0) return 0;
+  if (!r_sources || !vec_a || !out || !workspace) return fail(RMB_E_ARG, "null device pointer");
+  if (block == RMB_UF_UT && !vec_b) return fail(RMB_E_ARG, "RMB_UF_UT needs vec_b (torque)");
+  if (!(a > 0) || !(eta > 0)) return fail(RMB_E_ARG, "a and eta must be positive");
+  if ((reinterpret_cast<uintptr_t>(workspace) & 15) != 0) return fail(RMB_E_ARG, "workspace must be 16-byte aligned");
+  Call c;
+  c.block = block; c.wall = wall; c.precision = precision; c.flags = flags;
+  c.n_tgt = n_targets; c.n_src = n_sources; c.tgt_off = target_offset;
+  c.r = r_sources; c.va = vec_a; c.vb = vec_b; c.eta = eta; c.a = a;
+  for (int d = 0; d < 3; d++) c.L[d] = L ? L[d] : 0.0;
+  c.out = out; c.ws = static_cast<char*>(workspace); c.stream = static_cast<cudaStream_t>(stream);
+  const int rc = make_plan(block, precision, n_targets, n_sources, c.L, c.plan);
+  if (rc != 0) return rc;
+  if (workspace_bytes < c.plan.total) return fail(RMB_E_WORKSPACE, "workspace smaller than rmb_workspace_bytes()");
+  const bool per = c.L[0] > 0 || c.L[1] > 0 || c.L[2] > 0;
+  return precision == RMB_FP32 ? launch_block<float>(c, per) : launch_block<double>(c, per);
+}
+
+int rmb_fma_peak(int precision, int iters, double* flops, double* elapsed_ms)
+{
+  const int sms = sm_count();
+  if (sms <= 0) return sms;
+  if (iters <= 0 || !flops) return fail(RMB_E_ARG, "iters > 0 and flops != NULL required");
+  void* sink = nullptr;
+  cudaError_t e = cudaMalloc(&sink, 64);
+  if (e != cudaSuccess) return fail_cuda(e, "cudaMalloc");
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  const int blocks = sms * 8, threads = 256;
+  for (int rep = 0; rep < 2; rep++) {  // first pass warms up
+    cudaEventRecord(e0);
+    if (precision == RMB_FP32) fma_peak_kernel<float><<<blocks, threads>>>(iters, (float*)sink);
+    else fma_peak_kernel<double><<<blocks, threads>>>(iters, (double*)sink);
+    cudaEventRecord(e1);
+    e = cudaEventSynchronize(e1);
+    if (e != cudaSuccess) break;
+  }
+  float ms = 0;
+  if (e == cudaSuccess) cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaFree(sink);
+  if (e != cudaSuccess) return fail_cuda(e, "rmb_fma_peak");
+  *flops = 2.0 * 8.0 * (double)iters * blocks * threads / (ms * 1e-3);
+  if (elapsed_ms) *elapsed_ms = ms;
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,139 @@
+"""Host-side mirror of the reference's blob-mobility API for the B200 path.
+
+Every public function keeps the signature of its namesake in
+/root/reference/mobility/mobility.py,
+
+    f(r_vectors, vec, eta, a, *args, **kwargs) -> flat array of length 3N
+
+(`periodic_length` is the only kwarg read, mobility.py:1150), so that
+multi_bodies.set_mobility_vector_prod (multi_bodies/multi_bodies.py:233-287),
+QuaternionIntegratorRollers (quaternion_integrator_rollers.py:59-91) and the
+GMRES / Lanczos callers can select them as drop-in implementations:
+
+    reference name (numba / pycuda)                        here
+    single_wall_mobility_trans_times_force_{numba,pycuda}  single_wall_mobility_trans_times_force_b200
+    no_wall_mobility_rot_times_torque_{numba,pycuda}       no_wall_mobility_rot_times_torque_b200
+    single_wall_mobility_trans_times_force_torque_pycuda   single_wall_mobility_trans_times_force_torque_b200
+    ...
+
+Inputs may be NumPy arrays (uploaded, result downloaded: what SciPy callers
+need) or torch CUDA tensors (everything stays on the device: what the
+device-resident GMRES / Lanczos use).  Inputs are never modified.  Like the
+reference, nothing is raised for bad geometry (NaN/Inf come back); a missing
+CUDA extension or device DOES raise -- there is no CPU fallback.
+"""
+import ctypes
+import os
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import FP32, FP64, IN_PLANE, NO_TMA, NO_WALL, SINGLE_WALL, UF, UF_UT, UT, WF, WT  # noqa: F401
+
+_workspaces = {}
+default_flags = int(os.environ.get("RMB_FLAGS", "0"))  # OR-ed into every call (debug: RMB_FLAGS=2 -> RMB_NO_TMA)
+
+
+def _device(dev=None):
+    if not torch.cuda.is_available():
+        raise _lib.RmbError("rigidmultiblobswall_b200 needs a CUDA device (no CPU fallback)")
+    return torch.device("cuda", torch.cuda.current_device()) if dev is None else dev
+
+
+def _workspace(nbytes, dev):
+    ws = _workspaces.get(dev)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=dev)
+        _workspaces[dev] = ws
+    return ws
+
+
+def _as_device_f64(x, n3, dev):
+    """(N,3)/flat/strided NumPy or torch -> contiguous flat float64 CUDA tensor (a copy only if needed)."""
+    if isinstance(x, torch.Tensor):
+        t = x.to(device=dev, dtype=torch.float64).reshape(-1)
+    else:
+        t = torch.from_numpy(np.ascontiguousarray(np.asarray(x, dtype=np.float64).reshape(-1))).to(dev)
+    if t.numel() != n3:
+        raise ValueError("vector has %d entries, expected %d" % (t.numel(), n3))
+    return t.contiguous()
+
+
+def mobility_product(block, wall, r_vectors, vec, eta, a, periodic_length=None, vec_b=None,
+                     precision=FP64, flags=0, targets=None, out=None):
+    """out = rows `targets` of the (block, wall) blob mobility applied to vec.
+
+    targets = (offset, count) restricts the computed rows to a shard of the
+    blobs (multi-GPU: each rank owns a target range, sources are replicated).
+    """
+    lib = _lib.load()
+    host_in = not isinstance(r_vectors, torch.Tensor)
+    dev = _device(None if host_in else r_vectors.device)
+    n = (r_vectors.numel() if isinstance(r_vectors, torch.Tensor) else np.asarray(r_vectors).size) // 3
+    off, cnt = (0, n) if targets is None else targets
+    with torch.cuda.device(dev):
+        r = _as_device_f64(r_vectors, 3 * n, dev)
+        va = _as_device_f64(vec, 3 * n, dev)
+        vb = _as_device_f64(vec_b, 3 * n, dev) if block == UF_UT else None
+        L = np.zeros(3) if periodic_length is None else np.asarray(
+            periodic_length.cpu() if isinstance(periodic_length, torch.Tensor) else periodic_length, dtype=np.float64)
+        Lc = (ctypes.c_double * 3)(*[float(x) for x in L.reshape(-1)[:3]])
+        if out is None:
+            out = torch.empty(3 * cnt, dtype=torch.float64, device=dev)
+        if n > 0 and cnt > 0:
+            nbytes = lib.rmb_workspace_bytes(block, precision, cnt, n, Lc)
+            ws = _workspace(nbytes, dev)
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            _lib.check(lib.rmb_mobility_product(
+                block, wall, precision, flags | default_flags, cnt, n, off,
+                r.data_ptr(), va.data_ptr(), vb.data_ptr() if vb is not None else None,
+                float(eta), float(a), Lc, out.data_ptr(), ws.data_ptr(), ws.numel(), stream))
+        return out.cpu().numpy() if host_in else out
+
+
+def _make(block, wall, flags=0, precision=FP64, doc=""):
+    def f(r_vectors, vec, eta, a, *args, **kwargs):
+        return mobility_product(block, wall, r_vectors, vec, eta, a,
+                                periodic_length=kwargs.get("periodic_length"), precision=precision, flags=flags)
+    f.__doc__ = doc
+    return f
+
+
+def _make_fused(wall, precision=FP64, doc=""):
+    def f(r_vectors, force, torque, eta, a, *args, **kwargs):
+        return mobility_product(UF_UT, wall, r_vectors, force, eta, a, vec_b=torque,
+                                periodic_length=kwargs.get("periodic_length"), precision=precision)
+    f.__doc__ = doc
+    return f
+
+
+_TABLE = [
+    # name stem, block, wall, flags, reference lines in mobility/mobility.py (numba; pycuda)
+    ("no_wall_mobility_trans_times_force", UF, NO_WALL, 0, ":1119; :288"),
+    ("single_wall_mobility_trans_times_force", UF, SINGLE_WALL, 0, ":1132; :222"),
+    ("in_plane_mobility_trans_times_force", UF, SINGLE_WALL, IN_PLANE, ":1166; :255"),
+    ("no_wall_mobility_trans_times_torque", UT, NO_WALL, 0, ":1200; :482"),
+    ("single_wall_mobility_trans_times_torque", UT, SINGLE_WALL, 0, ":1213; :427"),
+    ("in_plane_mobility_trans_times_torque", UT, SINGLE_WALL, IN_PLANE, ":1235; :454"),
+    ("no_wall_mobility_rot_times_force", WF, NO_WALL, 0, ":1258; :328"),
+    ("single_wall_mobility_rot_times_force", WF, SINGLE_WALL, 0, ":1273; :300"),
+    ("no_wall_mobility_rot_times_torque", WT, NO_WALL, 0, ":1301; :370"),
+    ("single_wall_mobility_rot_times_torque", WT, SINGLE_WALL, 0, ":1316; :342"),
+]
+
+__all__ = ["mobility_product"]
+for _stem, _b, _w, _fl, _ref in _TABLE:
+    for _suffix, _prec in (("_b200", FP64), ("_b200_fp32", FP32)):
+        _name = _stem + _suffix
+        globals()[_name] = _make(_b, _w, _fl, _prec,
+                                 "B200 drop-in for mobility.%s_numba / _pycuda (mobility/mobility.py%s)." % (_stem, _ref))
+        globals()[_name].__name__ = _name
+        __all__.append(_name)
+for _wname, _w, _ref in (("single_wall", SINGLE_WALL, ":384"), ("no_wall", NO_WALL, ":413")):
+    for _suffix, _prec in (("_b200", FP64), ("_b200_fp32", FP32)):
+        _name = "%s_mobility_trans_times_force_torque%s" % (_wname, _suffix)
+        globals()[_name] = _make_fused(_w, _prec, "B200 drop-in for mobility.%s_mobility_trans_times_force_torque_pycuda "
+                                       "(mobility/mobility.py%s): UF f + UT t in one pass." % (_wname, _ref))
+        globals()[_name].__name__ = _name
+        __all__.append(_name)

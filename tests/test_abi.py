@@ -1,0 +1,56 @@
+"""CPU-side checks of the C-ABI library: it loads and exports every symbol
+include/rmb_mobility.h declares.  No compute calls (no GPU here)."""
+import ctypes
+import os
+import re
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    names = set()
+    for fn in os.listdir(os.path.join(ROOT, "include")):
+        txt = open(os.path.join(ROOT, "include", fn)).read()
+        txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+        names |= set(re.findall(r"\b(rmb_[a-z0-9_]+)\s*\(", txt))
+    return sorted(names)
+
+
+def test_library_exports_every_declared_symbol():
+    from rigidmultiblobswall_b200 import _build
+    so = _build.build()
+    lib = ctypes.CDLL(so)
+    decl = _declared()
+    assert "rmb_mobility_product" in decl and len(decl) >= 5
+    for name in decl:
+        assert hasattr(lib, name), name
+
+
+def test_version_and_argument_errors_without_gpu():
+    from rigidmultiblobswall_b200 import _lib
+    lib = _lib.load()
+    assert lib.rmb_version() == 100
+    # argument validation happens before any CUDA call
+    rc = lib.rmb_mobility_product(99, 0, 0, 0, 1, 1, 0, None, None, None, 1.0, 1.0, None, None, None, 0, None)
+    assert rc == -1 and b"block" in lib.rmb_last_error()
+    rc = lib.rmb_mobility_product(0, 0, 0, 0, 5, 4, 0, None, None, None, 1.0, 1.0, None, None, None, 0, None)
+    assert rc == -1 and b"target range" in lib.rmb_last_error()
+
+
+def test_python_api_mirrors_reference_names():
+    from rigidmultiblobswall_b200 import mobility as mb
+    for stem in ("no_wall_mobility_trans_times_force", "single_wall_mobility_trans_times_force",
+                 "in_plane_mobility_trans_times_force", "single_wall_mobility_trans_times_torque",
+                 "no_wall_mobility_rot_times_force", "single_wall_mobility_rot_times_torque",
+                 "single_wall_mobility_trans_times_force_torque"):
+        assert callable(getattr(mb, stem + "_b200"))
+        assert callable(getattr(mb, stem + "_b200_fp32"))
+
+
+def test_product_path_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "rigidmultiblobswall_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                txt = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in txt and "from oracle" not in txt and "mobility_oracle" not in txt, f

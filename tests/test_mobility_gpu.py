@@ -1,0 +1,198 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against
+ (1) the committed golden outputs of the reference's numba implementation,
+ (2) the CPU oracle (oracle/mobility_oracle.c) on seeded inputs,
+ (3) size-independent properties at large N.
+Tolerances are BASELINE.json's: 1e-12 relative (fp64), 1e-5 (fp32), norm-wise."""
+import os
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+TOL64, TOL32 = 1e-12, 1e-5
+BLOCK_ID = {"UF": 0, "UT": 1, "WF": 2, "WT": 3}
+
+
+def _cases():
+    g = np.load(os.path.join(HERE, "golden", "mf_golden.npz"))
+    return [str(c) for c in g["cases"]]
+
+
+def relerr(x, ref):
+    return np.linalg.norm(np.asarray(x) - ref) / np.linalg.norm(ref)
+
+
+@pytest.fixture(scope="module")
+def mb():
+    from rigidmultiblobswall_b200 import mobility
+    assert torch.cuda.is_available()
+    return mobility
+
+
+def _run(mb, case, golden, precision, flags=0):
+    cloud, lname, wall, blk = case.split("/")
+    r, v = golden[f"{cloud}/r"], golden[f"{cloud}/v"]
+    a, eta = golden[f"{cloud}/a_eta"]
+    L = golden[f"{cloud}/L_{lname}"]
+    fl = flags | (mb.IN_PLANE if wall == "in_plane" else 0)
+    w = mb.NO_WALL if wall == "no_wall" else mb.SINGLE_WALL
+    return mb.mobility_product(BLOCK_ID[blk], w, r, v, eta, a, periodic_length=L, precision=precision, flags=fl)
+
+
+@pytest.mark.parametrize("case", _cases())
+def test_golden_fp64(mb, golden, case):
+    out = _run(mb, case, golden, mb.FP64)
+    assert out.shape == golden[case].shape
+    assert relerr(out, golden[case]) < TOL64
+
+
+@pytest.mark.parametrize("case", [c for c in _cases() if "/open/" in c or "/xy/" in c])
+def test_golden_fp64_plain_loads(mb, golden, case):
+    """same kernels with the non-TMA tile loader (RMB_NO_TMA)"""
+    out = _run(mb, case, golden, mb.FP64, flags=mb.NO_TMA)
+    assert relerr(out, golden[case]) < TOL64
+
+
+@pytest.mark.parametrize("case", [c for c in _cases() if c.startswith(("dilute/", "c1/"))])
+def test_golden_fp32(mb, golden, case):
+    out = _run(mb, case, golden, mb.FP32)
+    assert relerr(out, golden[case]) < TOL32
+
+
+def test_named_wrappers_match_reference_signature(mb, golden):
+    r, v = golden["dense/r"], golden["dense/v"]
+    a, eta = golden["dense/a_eta"]
+    L = golden["dense/L_xy"]
+    u = mb.single_wall_mobility_trans_times_force_b200(r, v, eta, a, periodic_length=L)
+    assert isinstance(u, np.ndarray) and u.shape == (r.size,)
+    assert relerr(u, golden["dense/xy/single_wall/UF"]) < TOL64
+    # flat r_vectors, non-contiguous force slice, extra positional args are ignored like the reference
+    big = np.zeros((r.shape[0], 6)); big[:, :3] = v
+    u2 = mb.single_wall_mobility_trans_times_force_b200(r.flatten(), big[:, :3], eta, a, "ignored", periodic_length=L)
+    assert np.array_equal(u, u2)
+    w = mb.no_wall_mobility_rot_times_torque_b200(r, v, eta, a)
+    assert relerr(w, golden["dense/open/no_wall/WT"]) < TOL64
+    u32 = mb.single_wall_mobility_trans_times_force_b200_fp32(golden["dilute/r"], golden["dilute/v"],
+                                                              golden["dilute/a_eta"][1], golden["dilute/a_eta"][0])
+    assert relerr(u32, golden["dilute/open/single_wall/UF"]) < TOL32
+
+
+def test_inputs_not_mutated_and_torch_stays_on_device(mb, golden):
+    r, v = golden["dense/r"].copy(), golden["dense/v"].copy()
+    a, eta = golden["dense/a_eta"]
+    r0, v0 = r.copy(), v.copy()
+    mb.single_wall_mobility_trans_times_force_b200(r, v, eta, a)
+    assert np.array_equal(r, r0) and np.array_equal(v, v0)
+    rt, vt = torch.from_numpy(r).cuda(), torch.from_numpy(v).cuda()
+    ut = mb.single_wall_mobility_trans_times_force_b200(rt, vt, eta, a)
+    assert isinstance(ut, torch.Tensor) and ut.is_cuda and ut.dtype == torch.float64
+    assert relerr(ut.cpu().numpy(), golden["dense/open/single_wall/UF"]) < TOL64
+    assert torch.equal(rt.cpu(), torch.from_numpy(r0))
+
+
+@pytest.mark.parametrize("wall", ["single_wall", "no_wall"])
+@pytest.mark.parametrize("lname", ["open", "xy"])
+def test_fused_force_torque(mb, golden, wall, lname):
+    """fused UF f + UT t (mobility_pycuda.py:1266): oracle = sum of the two golden-checked products"""
+    r, f = golden["dense/r"], golden["dense/v"]
+    a, eta = golden["dense/a_eta"]
+    L = golden[f"dense/L_{lname}"]
+    t = f[::-1].copy()
+    import oracle
+    ref = golden[f"dense/{lname}/{wall}/UF"] + oracle.mobility_product("UT", wall, r, t, eta, a, L)
+    fn = getattr(mb, f"{wall}_mobility_trans_times_force_torque_b200")
+    assert relerr(fn(r, f, t, eta, a, periodic_length=L), ref) < TOL64
+
+
+@pytest.mark.parametrize("n", [1, 2, 31, 127, 128, 129, 255, 256, 257, 1000, 3001])
+def test_ragged_sizes_vs_oracle(mb, n):
+    """sizes around the CTA (128) and tile (256) boundaries, incl. N=1 (self term only)"""
+    import oracle
+    rng = np.random.default_rng(n)
+    a, eta = 0.21, 1.3
+    side = max(2.0, (n * 4 * np.pi / 3 / 0.15) ** (1 / 3)) * a
+    r = side * rng.random((n, 3)); r[:, 2] += 0.3 * a          # some blobs below z = a
+    v = rng.standard_normal((n, 3))
+    for blk in ("UF", "UT", "WF", "WT"):
+        ref = oracle.mobility_product(blk, "single_wall", r, v, eta, a)
+        out = mb.mobility_product(BLOCK_ID[blk], mb.SINGLE_WALL, r, v, eta, a)
+        assert relerr(out, ref) < TOL64, (blk, n)
+
+
+def test_empty_input(mb):
+    out = mb.single_wall_mobility_trans_times_force_b200(np.zeros((0, 3)), np.zeros((0, 3)), 1.0, 1.0)
+    assert out.shape == (0,)
+
+
+def test_source_split_path_vs_oracle(mb):
+    """N = 5000: too few target CTAs to fill the chip -> sources are split over blockIdx.y + finish kernel"""
+    import oracle
+    rng = np.random.default_rng(7)
+    n, a, eta = 5000, 0.5, 1.0
+    r = 40 * a * rng.random((n, 3)); r[:, 2] += 0.5 * a
+    v = rng.standard_normal((n, 3))
+    L = np.array([45 * a, 50 * a, 0.0])
+    for blk in ("UF", "WT"):
+        ref = oracle.mobility_product(blk, "single_wall", r, v, eta, a, L)
+        out = mb.mobility_product(BLOCK_ID[blk], mb.SINGLE_WALL, r, v, eta, a, periodic_length=L)
+        assert relerr(out, ref) < TOL64
+
+
+def test_target_shards_reassemble(mb, golden):
+    """multi-GPU decomposition on one device: target ranges computed separately give the full product"""
+    r, v = golden["c1/r"], golden["c1/v"]
+    a, eta = golden["c1/a_eta"]
+    full = mb.single_wall_mobility_trans_times_force_b200(r, v, eta, a)
+    parts = [mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, v, eta, a, targets=(o, c))
+             for o, c in ((0, 300), (300, 450), (750, 250))]
+    assert np.array_equal(np.concatenate(parts), full)
+    assert relerr(full, golden["c1/open/single_wall/UF"]) < TOL64
+
+
+def test_large_n_properties_and_sampled_oracle(mb):
+    """N = 60k (3.6e9 pairs): sampled rows against the oracle, linearity, UF symmetry f.(M g) = g.(M f)"""
+    import oracle
+    rng = np.random.default_rng(11)
+    n, a, eta = 60000, 0.13, 7.0
+    side = (n * 4 * np.pi / 3 / 0.1) ** (1 / 3) * a
+    r = side * rng.random((n, 3)); r[:, 2] += a
+    f, g = rng.standard_normal((n, 3)), rng.standard_normal((n, 3))
+    rt, ft, gt = (torch.from_numpy(x).cuda() for x in (r, f, g))
+    fn = mb.single_wall_mobility_trans_times_force_b200
+    uf, ug = fn(rt, ft, eta, a), fn(rt, gt, eta, a)
+    ufg = fn(rt, 2.0 * ft - 0.5 * gt, eta, a)
+    assert float(torch.linalg.norm(ufg - (2.0 * uf - 0.5 * ug)) / torch.linalg.norm(ufg)) < 1e-13
+    sym = abs(float(torch.dot(gt.reshape(-1), uf) - torch.dot(ft.reshape(-1), ug)))
+    assert sym / abs(float(torch.dot(gt.reshape(-1), uf))) < 1e-11
+    b, e = 31337, 31337 + 64
+    ref = oracle.mobility_product("UF", "single_wall", r, f, eta, a, targets=(b, e))
+    assert relerr(uf[3 * b:3 * e].cpu().numpy(), ref) < TOL64
+
+
+def test_transposition_identity_ut_wf(mb, golden):
+    """UT = WF^T: f.(UT t) = t.(WF f), with wall and images"""
+    r, f = golden["dense/r"], golden["dense/v"]
+    a, eta = golden["dense/a_eta"]
+    L = golden["dense/L_xy"]
+    z_ok = r.copy(); z_ok[:, 2] += a          # identity holds for the undamped operator
+    t = f[::-1].copy()
+    ut = mb.single_wall_mobility_trans_times_torque_b200(z_ok, t, eta, a, periodic_length=L)
+    wf = mb.single_wall_mobility_rot_times_force_b200(z_ok, f, eta, a, periodic_length=L)
+    lhs, rhs = np.dot(f.flatten(), ut), np.dot(t.flatten(), wf)
+    assert abs(lhs - rhs) / abs(lhs) < 1e-11
+
+
+def test_rsqrt_seed_accuracy_via_far_pairs(mb):
+    """two blobs far from each other and from the wall: u ~ Oseen; checks the MUFU.RSQ64H + cubic step end to end"""
+    import oracle
+    a, eta = 1.0, 1.0
+    rng = np.random.default_rng(3)
+    for scale in (1e0, 1e3, 1e6, 1e-2):
+        r = np.array([[0.0, 0.0, 5.0], [3.0 * scale + 3.0, 1.0, 7.0 * scale + 5.0]])
+        v = rng.standard_normal((2, 3))
+        ref = oracle.mobility_product("UF", "single_wall", r, v, eta, a)
+        out = mb.single_wall_mobility_trans_times_force_b200(r, v, eta, a)
+        assert np.max(np.abs(out - ref) / np.abs(ref)) < 1e-13
