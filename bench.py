@@ -79,17 +79,19 @@ class ClockSampler(threading.Thread):
 
 
 def cpu_reference_rate(r, f, a, eta, budget_s=12.0):
-    """The oracle (C/OpenMP port of mobility_numba) on a bounded sample: the first m targets against ALL sources."""
+    """The oracle's vectorised single-wall UF (C/OpenMP port of mobility_numba.py:124-287, all host threads) on a
+    bounded sample: the first m targets against ALL sources."""
     import oracle
     n = r.shape[0]
-    m = min(n, 64)
+    m = min(n, 256)
+    oracle.uf_wall_fast(r, f, eta, a, targets=(0, m))          # thread-pool warm-up
     t0 = time.perf_counter()
-    oracle.mobility_product("UF", "single_wall", r, f, eta, a, targets=(0, m))
+    oracle.uf_wall_fast(r, f, eta, a, targets=(0, m))
     dt = time.perf_counter() - t0
     rate = m * n / dt
     m2 = int(min(n, max(m, budget_s * rate / n)))
     t0 = time.perf_counter()
-    oracle.mobility_product("UF", "single_wall", r, f, eta, a, targets=(0, m2))
+    oracle.uf_wall_fast(r, f, eta, a, targets=(0, m2))
     dt = time.perf_counter() - t0
     return m2 * n / dt, oracle.threads(), "targets [0,%d) x all %d sources, %.1f s" % (m2, n, dt)
 
@@ -251,7 +253,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--n", type=int, default=1000000)
-    ap.add_argument("--ref-budget", type=float, default=8.0, help="seconds of CPU work per reference sample")
+    ap.add_argument("--ref-budget", type=float, default=12.0, help="seconds of CPU work per reference sample")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
     args = ap.parse_args()

@@ -54,6 +54,8 @@ def lib():
         _lib.rmb_oracle_wall_wrap.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_long, dp, dp,
                                               ctypes.c_double, ctypes.c_double, dp,
                                               ctypes.c_long, ctypes.c_long, dp]
+        _lib.rmb_oracle_uf_wall_fast.argtypes = [ctypes.c_long, dp, dp, ctypes.c_double, ctypes.c_double,
+                                                 ctypes.c_long, ctypes.c_long, dp]
         _lib.rmb_oracle_threads.restype = ctypes.c_int
     return _lib
 
@@ -87,4 +89,15 @@ def mobility_product(block, wall, r_vectors, vec, eta, a, periodic_length=None,
         lib().rmb_oracle_block(BLOCKS[block], 0, n, _p(r), _p(v), eta, a, _p(L), b, e, _p(out))
     else:
         raise ValueError(wall)
+    return out
+
+
+def uf_wall_fast(r_vectors, force, eta, a, targets=None):
+    """Vectorised timing variant of single-wall UF without images (the CPU baseline of bench.py)."""
+    r = np.ascontiguousarray(np.asarray(r_vectors, dtype=np.float64).reshape(-1, 3))
+    v = np.ascontiguousarray(np.asarray(force, dtype=np.float64).reshape(-1, 3))
+    n = r.shape[0]
+    b, e = (0, n) if targets is None else targets
+    out = np.empty(3 * (e - b))
+    lib().rmb_oracle_uf_wall_fast(n, _p(r), _p(v), eta, a, b, e, _p(out))
     return out

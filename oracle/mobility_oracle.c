@@ -358,3 +358,88 @@ int rmb_oracle_threads(void)
   return 1;
 #endif
 }
+
+/*
+ * Timing variant of the flagship block only (single-wall UF, no periodic
+ * images; mobility_numba.py:124-287): the same expressions as free_uf() +
+ * wall_uf() above, written branch-free over a structure-of-arrays copy so
+ * that gcc vectorises the source loop the way numba's fastmath LLVM build
+ * does (the reference's own numba build measured ~400 Mpairs/s on 8 threads
+ * in the build container; the scalar restatement above ~140).  Used by
+ * bench.py for the CPU baseline; checked against the golden vectors in
+ * tests/test_oracle.py like everything else in this file.
+ */
+void rmb_oracle_uf_wall_fast(long n, const double *r, const double *v, double eta, double a,
+                             long tgt_begin, long tgt_end, double *out)
+{
+  const double inva = 1.0 / a;
+  const double norm = 1.0 / (8.0 * M_PI * eta * a);
+  double *X = (double *)malloc(sizeof(double) * 6 * n);
+  double *Y = X + n, *Z = X + 2 * n, *FX = X + 3 * n, *FY = X + 4 * n, *FZ = X + 5 * n;
+  for (long k = 0; k < n; k++) {
+    const double z = r[3 * k + 2];
+    const double B = (z < a) ? z / a : 1.0;
+    X[k] = r[3 * k] * inva; Y[k] = r[3 * k + 1] * inva; Z[k] = ((z <= a) ? a : z) * inva;
+    FX[k] = B * v[3 * k]; FY[k] = B * v[3 * k + 1]; FZ[k] = B * v[3 * k + 2];
+  }
+#pragma omp parallel for schedule(static)
+  for (long i = tgt_begin; i < tgt_end; i++) {
+    const double xi = X[i], yi = Y[i], zi = Z[i];
+    double ux = 0, uy = 0, uz = 0;
+#pragma omp simd reduction(+ : ux, uy, uz)
+    for (long j = 0; j < n; j++) {
+      const double self = (j == i) ? 1.0 : 0.0;
+      const double rx = xi - X[j], ry = yi - Y[j], rz0 = zi - Z[j];
+      const double r2 = rx * rx + ry * ry + rz0 * rz0 + self;   /* keep the self lane finite */
+      const double rr = sqrt(r2);
+      const double invr = 1.0 / rr;
+      const double invr2 = invr * invr;
+      const int far = rr > 2;
+      const double c1 = far ? (1.0 + 2.0 / (3.0 * r2)) * invr : (4.0 / 3.0) * (1.0 - 0.28125 * rr);
+      const double c2 = far ? (1.0 - 2.0 * invr2) * invr2 * invr : (4.0 / 3.0) * 0.09375 * invr;
+      double Mxx = c1 + c2 * rx * rx, Mxy = c2 * rx * ry, Mxz = c2 * rx * rz0;
+      double Myy = c1 + c2 * ry * ry, Myz = c2 * ry * rz0, Mzz = c1 + c2 * rz0 * rz0;
+      double Myx = Mxy, Mzx = Mxz, Mzy = Myz;
+      const double rz = zi + Z[j];
+      const double hj = Z[j];
+      const double h_hat = hj / rz;
+      const double invR = 1.0 / sqrt(rx * rx + ry * ry + rz * rz);
+      const double ex = rx * invR, ey = ry * invR, ez = rz * invR;
+      const double invR3 = invR * invR * invR;
+      const double invR5 = invR3 * invR * invR;
+      const double fact1 = -(3.0 * (1.0 + 2.0 * h_hat * (1.0 - h_hat) * ez * ez) * invR + 2.0 * (1.0 - 3.0 * ez * ez) * invR3 - 2.0 * (1.0 - 5.0 * ez * ez) * invR5) / 3.0;
+      const double fact2 = -(3.0 * (1.0 - 6.0 * h_hat * (1.0 - h_hat) * ez * ez) * invR - 6.0 * (1.0 - 5.0 * ez * ez) * invR3 + 10.0 * (1.0 - 7.0 * ez * ez) * invR5) / 3.0;
+      const double fact3 = ez * (3.0 * h_hat * (1.0 - 6.0 * (1.0 - h_hat) * ez * ez) * invR - 6.0 * (1.0 - 5.0 * ez * ez) * invR3 + 10.0 * (2.0 - 7.0 * ez * ez) * invR5) * 2.0 / 3.0;
+      const double fact4 = ez * (3.0 * h_hat * invR - 10.0 * invR5) * 2.0 / 3.0;
+      const double fact5 = -(3.0 * h_hat * h_hat * ez * ez * invR + 3.0 * ez * ez * invR3 + (2.0 - 15.0 * ez * ez) * invR5) * 4.0 / 3.0;
+      Mxx += fact1 + fact2 * ex * ex;
+      Mxy += fact2 * ex * ey;
+      Mxz += fact2 * ex * ez + fact3 * ex;
+      Myx += fact2 * ey * ex;
+      Myy += fact1 + fact2 * ey * ey;
+      Myz += fact2 * ey * ez + fact3 * ey;
+      Mzx += fact2 * ez * ex + fact4 * ex;
+      Mzy += fact2 * ez * ey + fact4 * ey;
+      Mzz += fact1 + fact2 * ez * ez + fact3 * ez + fact4 * ez + fact5;
+      const double m = 1.0 - self;   /* the self pair is added in closed form below */
+      const double fx = FX[j] * m, fy = FY[j] * m, fz = FZ[j] * m;
+      ux += Mxx * fx + Mxy * fy + Mxz * fz;
+      uy += Myx * fx + Myy * fy + Myz * fz;
+      uz += Mzx * fx + Mzy * fy + Mzz * fz;
+    }
+    {
+      const double invZi = 1.0 / zi;
+      const double invZi3 = invZi * invZi * invZi;
+      const double invZi5 = invZi3 * invZi * invZi;
+      const double sxx = 4.0 / 3.0 - (9.0 * invZi - 2.0 * invZi3 + invZi5) / 12.0;
+      const double szz = 4.0 / 3.0 - (9.0 * invZi - 4.0 * invZi3 + invZi5) / 6.0;
+      ux += sxx * FX[i]; uy += sxx * FY[i]; uz += szz * FZ[i];
+    }
+    const double z = r[3 * i + 2];
+    const double B = ((z < a) ? z / a : 1.0) * norm;
+    out[3 * (i - tgt_begin)] = ux * B;
+    out[3 * (i - tgt_begin) + 1] = uy * B;
+    out[3 * (i - tgt_begin) + 2] = uz * B;
+  }
+  free(X);
+}

@@ -36,3 +36,13 @@ def test_oracle_target_subset(golden):
     full = oracle.mobility_product("UF", "single_wall", r, v, eta, a)
     part = oracle.mobility_product("UF", "single_wall", r, v, eta, a, targets=(17, 60))
     assert np.array_equal(full[3 * 17:3 * 60], part)
+
+
+@pytest.mark.parametrize("cloud", ["dense", "dilute", "c1"])
+def test_vectorised_timing_variant_matches_reference_numba(golden, cloud):
+    r, v = golden[f"{cloud}/r"], golden[f"{cloud}/v"]
+    a, eta = golden[f"{cloud}/a_eta"]
+    out = oracle.uf_wall_fast(r, v, eta, a)
+    assert relerr(out, golden[f"{cloud}/open/single_wall/UF"]) < 1e-13
+    part = oracle.uf_wall_fast(r, v, eta, a, targets=(5, 40))
+    assert np.array_equal(part, out[15:120])
