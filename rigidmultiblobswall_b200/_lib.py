@@ -23,9 +23,10 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(_build.SO):
+    so = os.environ.get("RMB_LIB") or _build.SO      # RMB_LIB: tuning builds (tools/tune.sh)
+    if not os.path.exists(so):
         _build.build()
-    lib = ctypes.CDLL(_build.SO)
+    lib = ctypes.CDLL(so)
     c_dp = ctypes.c_void_p
     lib.rmb_version.restype = ctypes.c_int
     lib.rmb_last_error.restype = ctypes.c_char_p

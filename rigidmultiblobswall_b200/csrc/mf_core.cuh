@@ -105,7 +105,7 @@ RMB_HD void pair_geometry(const Target<T>& t, T xj, T yj, T zj, const Periodic<T
 template <typename T, int BLOCK, bool WALL>
 RMB_HD void pair_apply(const PairGeom<T>& g, T ht, const T* v, bool any_near, T r2, T rxy2, T& ux, T& uy, T& uz)
 {
-  if (BLOCK == UF || BLOCK == UF_UT) pair_uf<T, WALL>(g, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
+  if (BLOCK == UF || BLOCK == UF_UT) pair_uf<T, WALL>(g, ht, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
   if (BLOCK == WF) pair_wf<T, WALL>(g, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
   if (BLOCK == WT) pair_wt<T, WALL>(g, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
   if (BLOCK == UT || BLOCK == UF_UT) {

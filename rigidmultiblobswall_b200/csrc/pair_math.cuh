@@ -78,12 +78,22 @@ struct PairGeom {
 //   far  (r > 2):  [ (1 + 2/(3r^2)) I + (1 - 2/r^2) rr/r^2 ] / r
 //   near (r <= 2): 4/3 [ (1 - 9r/32) I + 3/(32 r) rr ]
 // Wall correction (:242-276), Swan & Brady fact1..5 with e = R/|R|,
-// R = (rx, ry, Rz), g = h_hat*ez = h/|R|:
+// R = (rx, ry, Rz):
 //   u += fact1 f + e (fact2 (e.f) + fact3 f_z) + z^ (fact4 (e.f) + fact5 f_z)
-// ANY_NEAR: warp-uniform flag "some lane of this warp has r2 < 4" -- the near
+// Rewritten with q = 1/|R|, t = q^2, alpha = Rz^2, beta = h_i h_j, k = alpha t
+// (= ez^2), H = h_j; h_hat(1-h_hat)ez^2 = beta t and h_hat ez = H q, so
+//   fact1 = q p1, fact2 = q p2, fact3 = q^2 p3, fact4 = q^2 p4, fact5 = q^3 p5
+//   p1 = -1 - (2 beta + 2/3) t + (2 alpha + 2/3) t^2 - (10/3) k t^2
+//   p2 = -1 + (6 beta + 2) t - (10 alpha + 10/3) t^2 + (70/3) k t^2
+//   p3 = 2H - Rz t [ (12 beta + 4) - (20 alpha + 40/3) t + (140/3) k t ]
+//   p4 = 2H - (20/3) Rz t^2
+//   p5 = -4H^2 - (4 alpha + 8/3) t + 20 k t
+//   u += q p1 f + q^3 [ (p2 (R.f) + p3 f_z) R + z^ (p4 (R.f) + p5 f_z) ]
+// 71 FP64 instructions per far pair in total (was 203 flop as the reference
+// writes it).  any_near: warp-uniform flag "some lane has r2 < 4" -- the near
 // coefficients are only evaluated when it is set.
 template <typename T, bool WALL>
-RMB_HD void pair_uf(const PairGeom<T>& p, T fx, T fy, T fz, bool any_near, T r2, T rxy2, T& ux, T& uy, T& uz)
+RMB_HD void pair_uf(const PairGeom<T>& p, T ht, T fx, T fy, T fz, bool any_near, T r2, T rxy2, T& ux, T& uy, T& uz)
 {
   const T s = RMB_FMA(p.ry, fy, p.rx * fx);
   const T invr = rsqrt_full(r2);
@@ -101,41 +111,38 @@ RMB_HD void pair_uf(const PairGeom<T>& p, T fx, T fy, T fz, bool any_near, T r2,
     A = near ? An : A;
     B = near ? Bn : B;
   }
-  ux = RMB_FMA(A, fx, ux); uy = RMB_FMA(A, fy, uy); uz = RMB_FMA(A, fz, uz);
-  ux = RMB_FMA(B, p.rx, ux); uy = RMB_FMA(B, p.ry, uy); uz = RMB_FMA(B, p.rz, uz);
-  if (WALL) {
-    const T R2 = RMB_FMA(p.Rz, p.Rz, rxy2);
-    const T q = rsqrt_full(R2);
-    const T q2 = q * q;
-    const T ez = p.Rz * q;
-    const T g = p.h * q;
-    const T ez2 = ez * ez;
-    const T d = ez - g;
-    const T w = g * d;
+  if (!WALL) {
+    ux = RMB_FMA(A, fx, ux); uy = RMB_FMA(A, fy, uy); uz = RMB_FMA(A, fz, uz);
+    ux = RMB_FMA(B, p.rx, ux); uy = RMB_FMA(B, p.ry, uy); uz = RMB_FMA(B, p.rz, uz);
+  } else {
+    const T al = p.Rz * p.Rz;
+    const T q = rsqrt_full(rxy2 + al);
+    const T t = q * q;
+    const T q3 = q * t;
+    const T be = ht * p.h;
+    const T k = al * t;
+    T p1 = RMB_FMA(T(-10.0 / 3.0), k, RMB_FMA(T(2.0), al, T(2.0 / 3.0)));
+    p1 = RMB_FMA(p1, t, -RMB_FMA(T(2.0), be, T(2.0 / 3.0)));
+    p1 = RMB_FMA(p1, t, T(-1.0));
+    T p2 = RMB_FMA(T(70.0 / 3.0), k, -RMB_FMA(T(10.0), al, T(10.0 / 3.0)));
+    p2 = RMB_FMA(p2, t, RMB_FMA(T(6.0), be, T(2.0)));
+    p2 = RMB_FMA(p2, t, T(-1.0));
+    T i3 = RMB_FMA(T(-140.0 / 3.0), k, RMB_FMA(T(20.0), al, T(40.0 / 3.0)));
+    i3 = RMB_FMA(i3, t, -RMB_FMA(T(12.0), be, T(4.0)));
+    const T Zt = p.Rz * t;
+    const T H2 = p.h + p.h;
+    const T p3 = RMB_FMA(i3, Zt, H2);
+    const T p4 = RMB_FMA(T(-20.0 / 3.0) * Zt, t, H2);
+    T p5 = RMB_FMA(T(20.0), k, -RMB_FMA(T(4.0), al, T(8.0 / 3.0)));
+    p5 = RMB_FMA(p5, t, -(H2 * H2));
     const T Rf = RMB_FMA(p.Rz, fz, s);
-    const T ef = Rf * q;
-    // m_k = fact_k / q as polynomials in q2 (Horner)
-    T m1 = RMB_FMA(T(-10.0 / 3.0), ez2, T(2.0 / 3.0));
-    m1 = RMB_FMA(m1, q2, RMB_FMA(T(2.0), ez2, T(-2.0 / 3.0)));
-    m1 = RMB_FMA(m1, q2, RMB_FMA(T(-2.0), w, T(-1.0)));
-    T m2 = RMB_FMA(T(70.0 / 3.0), ez2, T(-10.0 / 3.0));
-    m2 = RMB_FMA(m2, q2, RMB_FMA(T(-10.0), ez2, T(2.0)));
-    m2 = RMB_FMA(m2, q2, RMB_FMA(T(6.0), w, T(-1.0)));
-    T m3 = RMB_FMA(T(-140.0 / 3.0), ez2, T(40.0 / 3.0));
-    m3 = RMB_FMA(m3, q2, RMB_FMA(T(20.0), ez2, T(-4.0)));
-    m3 = (m3 * q2) * ez;
-    m3 = RMB_FMA(g, RMB_FMA(T(-12.0), ez * d, T(2.0)), m3);
-    const T q4 = q2 * q2;
-    const T m4 = RMB_FMA(T(-20.0 / 3.0), ez * q4, g + g);
-    T m5 = RMB_FMA(T(20.0), ez2, T(-8.0 / 3.0));
-    m5 = RMB_FMA(T(-4.0), ez2, m5 * q2);
-    m5 = RMB_FMA(T(-4.0), g * g, m5 * q2);
-    const T f1 = m1 * q;
-    const T P = RMB_FMA(m2, ef, m3 * fz) * q2;        // (fact2 (e.f) + fact3 fz) / |R|
-    const T Z = RMB_FMA(m4, ef, m5 * fz) * q;         // fact4 (e.f) + fact5 fz
-    ux = RMB_FMA(f1, fx, ux); uy = RMB_FMA(f1, fy, uy); uz = RMB_FMA(f1, fz, uz);
-    ux = RMB_FMA(P, p.rx, ux); uy = RMB_FMA(P, p.ry, uy); uz = RMB_FMA(P, p.Rz, uz);
-    uz += Z;
+    const T SR = RMB_FMA(p2, Rf, p3 * fz) * q3;
+    const T SZ = RMB_FMA(p4, Rf, p5 * fz);
+    const T Af = RMB_FMA(q, p1, A);
+    const T Bx = B + SR;
+    ux = RMB_FMA(Af, fx, ux); uy = RMB_FMA(Af, fy, uy); uz = RMB_FMA(Af, fz, uz);
+    ux = RMB_FMA(Bx, p.rx, ux); uy = RMB_FMA(Bx, p.ry, uy);
+    uz = RMB_FMA(B, p.rz, uz); uz = RMB_FMA(SR, p.Rz, uz); uz = RMB_FMA(q3, SZ, uz);
   }
 }
 

@@ -23,9 +23,27 @@ using namespace rmb;
 
 namespace {
 
-constexpr int TPB = 128;    // targets (threads) per CTA
-constexpr int TILE = 256;   // sources per shared-memory tile
+// Tuning knobs (defaults = the configuration measured best on B200)
+#ifndef RMB_TPB
+#define RMB_TPB 128
+#endif
+#ifndef RMB_TILE
+#define RMB_TILE 256
+#endif
+#ifndef RMB_UNROLL
+#define RMB_UNROLL 2
+#endif
+#ifndef RMB_MINB
+#define RMB_MINB 1
+#endif
+#ifndef RMB_WAVES
+#define RMB_WAVES 10
+#endif
+constexpr int TPB = RMB_TPB;    // targets (threads) per CTA
+constexpr int TILE = RMB_TILE;  // sources per shared-memory tile
 constexpr int STAGES = 2;
+#define RMB_PRAGMA(x) _Pragma(#x)
+#define RMB_UNROLL_N(n) RMB_PRAGMA(unroll n)
 
 thread_local char g_err[512] = "";
 
@@ -168,7 +186,7 @@ __device__ __forceinline__ void tile_pairs(const T* __restrict__ tile, int cnt, 
 {
   constexpr int NV = (BLOCK == UF_UT) ? 2 : 1;
   constexpr int W = RecWords<T, NV>::value;
-#pragma unroll 2
+RMB_UNROLL_N(RMB_UNROLL)
   for (int j = 0; j < cnt; j++) {
     T w[W];
     load_rec<W>(tile + j * W, w);
@@ -187,7 +205,7 @@ __device__ __forceinline__ void tile_pairs(const T* __restrict__ tile, int cnt, 
 }
 
 template <typename T, int BLOCK, bool WALL, bool PERIODIC, bool TMA>
-__global__ void __launch_bounds__(TPB) mf_kernel(const __grid_constant__ MfArgs<T, (BLOCK == UF_UT) ? 2 : 1> A)
+__global__ void __launch_bounds__(TPB, RMB_MINB) mf_kernel(const __grid_constant__ MfArgs<T, (BLOCK == UF_UT) ? 2 : 1> A)
 {
   constexpr int NV = (BLOCK == UF_UT) ? 2 : 1;
   constexpr int W = RecWords<T, NV>::value;
@@ -336,9 +354,12 @@ int make_plan(int block, int precision, long n_tgt, long n_src, const double* L,
   if (L) for (int d = 0; d < 3; d++) if (L[d] > 0) p.n_boxes *= 3;
   p.n_vt = p.n_tiles * p.n_boxes;
   p.tgt_blocks = (int)((n_tgt + TPB - 1) / TPB);
-  const int want = sms * 8;
-  int split = (want + p.tgt_blocks - 1) / p.tgt_blocks;
-  if (split > p.n_vt) split = p.n_vt;
+  // Source splitting (blockIdx.y): used when the target CTAs alone would give
+  // fewer than RMB_WAVES waves of resident CTAs (tail effect / idle SMs).  A
+  // split keeps >= 4 tiles so the prologue stays amortised.
+  const int resident = sms * (768 / TPB);
+  int split = (RMB_WAVES * resident + p.tgt_blocks - 1) / p.tgt_blocks;
+  if (split > p.n_vt / 4) split = p.n_vt / 4;
   if (split < 1) split = 1;
   p.vt_per_split = (p.n_vt + split - 1) / split;
   p.n_split = (p.n_vt + p.vt_per_split - 1) / p.vt_per_split;
