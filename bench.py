@@ -107,7 +107,7 @@ def run_reference(args):
         if it >= args.warmup:
             times.append(rate)
     v = float(np.mean(times))
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "pairs/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * args.n * args.n / v,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -115,7 +115,7 @@ def run_reference(args):
                    "note": "CPU port of mobility_numba (oracle/, C+OpenMP); ms_per_step extrapolated from the sample"},
         "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
 
 
 def run_b200(args):
@@ -241,12 +241,25 @@ def run_b200(args):
             "clocks": clocks,
             "parity_rel_err_vs_oracle": parity,
         }
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+def emit(line):
+    """The ONE JSON line, on the real stdout (fd 1 is pointed at stderr while the run is in progress so
+    that library chatter such as NCCL's version banner cannot land in front of it)."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)

@@ -1,0 +1,206 @@
+"""Rigid-body operators on the device: K, K^T, the saddle-point operator of
+the mobility problem and the block-diagonal preconditioner.
+
+Mirrors (same names, same argument meaning) the module-level functions of
+/root/reference/multi_bodies/multi_bodies.py that run inside every GMRES
+iteration as interpreted loops over bodies:
+
+    K_matrix_vector_prod              multi_bodies.py:328-347
+    K_matrix_T_vector_prod            multi_bodies.py:350-371
+    linear_operator_rigid             multi_bodies.py:424-471  (no constraints, no prescribed kinematics)
+    build_block_diagonal_preconditioner  multi_bodies.py:752-903 (free bodies)
+    get_blobs_r_vectors               multi_bodies.py:196-208 / body.py:64-80
+
+The `bodies` argument is a RigidBodies object (the device-resident form of
+the reference's list of body.Body); vectors are torch CUDA float64 tensors.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib, mobility
+
+
+def _rlib():
+    lib = _lib.load()
+    if not getattr(lib, "_rigid_bound", False):
+        vp, cl, cd, ci = ctypes.c_void_p, ctypes.c_long, ctypes.c_double, ctypes.c_int
+        lib.rmb_rigid_last_error.restype = ctypes.c_char_p
+        lib.rmb_blobs_from_bodies.argtypes = [cl, vp, vp, vp, vp, vp, vp]
+        lib.rmb_K_apply.argtypes = [cl, vp, vp, vp, vp, cd, cd, vp, vp]
+        lib.rmb_KT_apply.argtypes = [cl, vp, vp, vp, vp, cd, vp, vp]
+        lib.rmb_body_mobility_blocks.argtypes = [cl, vp, ci, vp, cd, cd, ci, vp, vp]
+        lib._rigid_bound = True
+    return lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise _lib.RmbError("librmb_mobility (rigid): error %d: %s" % (rc, _rlib().rmb_rigid_last_error().decode()))
+
+
+def _stream(dev):
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+class RigidBodies:
+    """Device-resident suspension: for every body its location, quaternion
+    (s, p1, p2, p3) and reference configuration (body/body.py:17-40).  Body b
+    owns the contiguous blob range [body_offset[b], body_offset[b+1])."""
+
+    def __init__(self, reference_configurations, locations, quaternions, device=None):
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.device = dev
+        if isinstance(reference_configurations, np.ndarray) and reference_configurations.ndim == 2:
+            reference_configurations = [reference_configurations] * len(locations)
+        counts = np.array([len(c) for c in reference_configurations], dtype=np.int64)
+        self.n_bodies = len(counts)
+        self.n_blobs = int(counts.sum())
+        self.nb_max = int(counts.max()) if self.n_bodies else 0
+        self.uniform = bool(self.n_bodies and (counts == counts[0]).all())
+        off = np.zeros(self.n_bodies + 1, dtype=np.int64)
+        np.cumsum(counts, out=off[1:])
+        self.counts = counts
+        self.body_offset_host = off
+        self.body_offset = torch.from_numpy(off).to(dev)
+        self.blob_body = torch.from_numpy(np.repeat(np.arange(self.n_bodies, dtype=np.int32), counts)).to(dev)
+        ref = np.concatenate([np.asarray(c, dtype=np.float64).reshape(-1, 3) for c in reference_configurations]) \
+            if self.n_bodies else np.zeros((0, 3))
+        self.reference_configuration = torch.from_numpy(np.ascontiguousarray(ref)).to(dev)
+        self.location = torch.as_tensor(np.asarray(locations, dtype=np.float64).reshape(-1, 3)).to(dev).contiguous()
+        self.quaternion = torch.as_tensor(np.asarray(quaternions, dtype=np.float64).reshape(-1, 4)).to(dev).contiguous()
+
+    @classmethod
+    def from_bodies(cls, bodies, device=None):
+        """From the reference's own list of body.Body objects."""
+        return cls([b.reference_configuration for b in bodies], [b.location for b in bodies],
+                   [b.orientation.entries for b in bodies], device=device)
+
+    def get_r_vectors(self):
+        """multi_bodies.get_blobs_r_vectors (multi_bodies.py:196-208): flat 3*Nblobs tensor."""
+        r = torch.empty(3 * self.n_blobs, dtype=torch.float64, device=self.device)
+        _check(_rlib().rmb_blobs_from_bodies(self.n_blobs, self.blob_body.data_ptr(),
+                                             self.reference_configuration.data_ptr(), self.location.data_ptr(),
+                                             self.quaternion.data_ptr(), r.data_ptr(), _stream(self.device)))
+        return r
+
+
+def get_blobs_r_vectors(bodies, Nblobs=None):
+    return bodies.get_r_vectors()
+
+
+def K_matrix_vector_prod(bodies, vector, Nblobs=None, K_bodies=None, r_vectors=None, out=None, alpha=1.0, beta=0.0):
+    """K * vector: (U_b, omega_b) per body -> blob velocities U_b + omega_b x (r_i - q_b); returns (Nblobs, 3).
+    out/alpha/beta give the fused update out = beta*out + alpha*K*vector."""
+    r = bodies.get_r_vectors() if r_vectors is None else r_vectors
+    U = vector.reshape(-1).contiguous()
+    if out is None:
+        out = torch.empty(3 * bodies.n_blobs, dtype=torch.float64, device=bodies.device)
+        beta = 0.0
+    _check(_rlib().rmb_K_apply(bodies.n_blobs, bodies.blob_body.data_ptr(), r.data_ptr(), bodies.location.data_ptr(),
+                               U.data_ptr(), float(alpha), float(beta), out.data_ptr(), _stream(bodies.device)))
+    return out.view(-1, 3)
+
+
+def K_matrix_T_vector_prod(bodies, vector, Nblobs=None, K_bodies=None, r_vectors=None, alpha=1.0):
+    """K^T * vector: blob forces -> (force, torque) per body; returns (2*Nbodies, 3) like the reference."""
+    r = bodies.get_r_vectors() if r_vectors is None else r_vectors
+    lam = vector.reshape(-1).contiguous()
+    out = torch.empty(6 * bodies.n_bodies, dtype=torch.float64, device=bodies.device)
+    _check(_rlib().rmb_KT_apply(bodies.n_bodies, bodies.body_offset.data_ptr(), r.data_ptr(),
+                                bodies.location.data_ptr(), lam.data_ptr(), float(alpha), out.data_ptr(),
+                                _stream(bodies.device)))
+    return out.view(-1, 3)
+
+
+def linear_operator_rigid(vector, bodies, r_vectors, eta, a, mobility_vector_prod=None, *args, **kwargs):
+    """Action of  |  M   -K | on [lambda; U]  (multi_bodies.py:424-471, free bodies, no constraints).
+                  | -K^T  0 |
+    mobility_vector_prod defaults to the single-wall B200 product."""
+    mvp = mobility.single_wall_mobility_trans_times_force_b200 if mobility_vector_prod is None else mobility_vector_prod
+    n3 = 3 * bodies.n_blobs
+    res = torch.empty_like(vector)
+    lam, U = vector[:n3], vector[n3:]
+    res[:n3] = mvp(r_vectors, lam, eta, a, *args, **kwargs)
+    K_matrix_vector_prod(bodies, U, r_vectors=r_vectors, out=res[:n3], alpha=-1.0, beta=1.0)
+    res[n3:] = K_matrix_T_vector_prod(bodies, lam, r_vectors=r_vectors, alpha=-1.0).reshape(-1)
+    return res
+
+
+class BlockDiagonalPreconditioner:
+    """Block-diagonal preconditioner of the mobility problem on the device.
+
+    build (multi_bodies.py:766-785), per body b:
+        M_b  dense blob mobility of the body alone (rmb_body_mobility_blocks)
+        M_b^-1  via batched Cholesky (torch.linalg.cholesky + cholesky_inverse: plain library calls)
+        N_b = pinv(K_b^T M_b^-1 K_b)   (6x6)
+    apply (multi_bodies.py:825-846), per body:
+        Lambda~ = M_b^-1 slip;  U = N_b (-F - K^T Lambda~);  Lambda = M_b^-1 (slip + K U)
+    Bodies with fewer blobs than nb_max are identity-padded (the padding rows
+    never couple to real ones)."""
+
+    def __init__(self, bodies, r_vectors, eta, a, wall=True):
+        self.bodies = bodies
+        dev = bodies.device
+        nb, m = bodies.n_bodies, 3 * bodies.nb_max
+        self.m = m
+        M = torch.empty(nb, m, m, dtype=torch.float64, device=dev)
+        r = r_vectors.reshape(-1).contiguous()
+        lib = _rlib()
+        for b0 in range(0, nb, 65535):
+            b1 = min(nb, b0 + 65535)
+            _check(lib.rmb_body_mobility_blocks(b1 - b0, bodies.body_offset[b0:].data_ptr(), bodies.nb_max,
+                                                r.data_ptr(), float(eta), float(a), int(bool(wall)),
+                                                M[b0:].data_ptr(), _stream(dev)))
+        self.M_blobs = M
+        self.chol = torch.linalg.cholesky(M)
+        self.M_inv = torch.cholesky_inverse(self.chol)
+        # padded gather/scatter maps between the flat blob vector and [nb, 3 nb_max]
+        if bodies.uniform:
+            self.pad_index = None
+        else:
+            idx = torch.full((nb, m), 3 * bodies.n_blobs, dtype=torch.int64, device=dev)   # -> appended zero
+            off, cnt = bodies.body_offset_host, bodies.counts
+            rows = np.repeat(np.arange(nb), 3 * cnt)
+            cols = np.concatenate([np.arange(3 * c) for c in cnt])
+            idx[torch.from_numpy(rows).to(dev), torch.from_numpy(cols).to(dev)] = torch.arange(
+                3 * bodies.n_blobs, device=dev)
+            self.pad_index = idx
+            self.valid = idx < 3 * bodies.n_blobs
+        # dense K per body [nb, 3 nb_max, 6] (columns = K applied to unit rigid motions)
+        K = torch.zeros(nb, m, 6, dtype=torch.float64, device=dev)
+        for c in range(6):
+            U = torch.zeros(nb, 6, dtype=torch.float64, device=dev)
+            U[:, c] = 1.0
+            K[:, :, c] = self._pad(K_matrix_vector_prod(bodies, U, r_vectors=r).reshape(-1))
+        self.K = K
+        self.N = torch.linalg.pinv(K.transpose(1, 2) @ self.M_inv @ K, hermitian=True)
+
+    def _pad(self, flat):
+        if self.pad_index is None:
+            return flat.reshape(self.bodies.n_bodies, self.m)
+        ext = torch.cat([flat, flat.new_zeros(1)])
+        return ext[self.pad_index]
+
+    def _unpad(self, padded):
+        if self.pad_index is None:
+            return padded.reshape(-1)
+        return padded[self.valid]
+
+    def __call__(self, vector):
+        nb, n3 = self.bodies.n_bodies, 3 * self.bodies.n_blobs
+        slip = self._pad(vector[:n3]).unsqueeze(2)                 # [nb, m, 1]
+        F = vector[n3:].reshape(nb, 6, 1)
+        lam_t = self.M_inv @ slip
+        U = self.N @ (-F - self.K.transpose(1, 2) @ lam_t)
+        lam = self.M_inv @ (slip + self.K @ U)
+        out = torch.empty_like(vector)
+        out[:n3] = self._unpad(lam.squeeze(2))
+        out[n3:] = U.reshape(-1)
+        return out
+
+
+def build_block_diagonal_preconditioner(bodies, r_vectors, Nblobs, eta, a, *args, **kwargs):
+    """Same role as multi_bodies.build_block_diagonal_preconditioner (multi_bodies.py:752): returns the callable."""
+    return BlockDiagonalPreconditioner(bodies, r_vectors, eta, a, wall=kwargs.get("wall", True))
