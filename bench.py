@@ -36,6 +36,50 @@ def make_cloud(n, seed=1234):
     return r, f, a, eta
 
 
+def make_c2(n_bodies=1000, seed=77):
+    """BASELINE config 2: boomerang_N_15 bodies on a grid with spacing 4.0, heights in [3,4),
+    random unit quaternions, a = 0.25, eta = 1, tolerance 1e-8 (multi_bodies/inputfile.dat)."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "rigid_golden.npz"))
+    rng = np.random.default_rng(seed)
+    side = int(np.ceil(np.sqrt(n_bodies)))
+    k = np.arange(n_bodies)
+    loc = np.stack([4.0 * (k % side), 4.0 * (k // side), 3.0 + rng.random(n_bodies)], axis=1)
+    quat = rng.standard_normal((n_bodies, 4))
+    quat /= np.linalg.norm(quat, axis=1)[:, None]
+    FT = rng.standard_normal(6 * n_bodies)
+    return g["struct/boomerang_N_15"], loc, quat, FT, 0.25, 1.0, 1e-8
+
+
+def gmres_mobility_solve(n_bodies=1000, repeats=3):
+    """Secondary metric: wall seconds of the config-2 mobility solve (preconditioner build + GMRES), device
+    resident, timed with CUDA events after one warm-up solve."""
+    import torch
+    from rigidmultiblobswall_b200 import rigid
+    ref_cfg, loc, quat, FT, a, eta, tol = make_c2(n_bodies)
+    bodies = rigid.RigidBodies(ref_cfg, loc, quat)
+    out = None
+    times = []
+    for it in range(repeats + 1):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        vel, lam, its, info = rigid.solve_mobility_problem(bodies, FT, eta, a, tolerance=tol)
+        e1.record()
+        torch.cuda.synchronize()
+        if it > 0:
+            times.append(e0.elapsed_time(e1) * 1e-3)
+        out = (vel, lam, its, info)
+    vel, lam, its, info = out
+    r = bodies.get_r_vectors()
+    x = torch.cat([lam.reshape(-1), vel.reshape(-1)])
+    rhs = torch.cat([torch.zeros(3 * bodies.n_blobs, dtype=torch.float64, device=x.device),
+                     -torch.from_numpy(FT).to(x.device)])
+    res = float(torch.linalg.norm(rigid.linear_operator_rigid(x, bodies, r, eta, a) - rhs) / torch.linalg.norm(rhs))
+    return {"seconds": float(np.median(times)), "unit": "s", "bodies": n_bodies, "blobs": bodies.n_blobs,
+            "iterations": int(its), "info": int(info), "tolerance": tol, "true_residual": res,
+            "includes": "block-diagonal preconditioner build + GMRES(60), device resident"}
+
+
 class ClockSampler(threading.Thread):
     """Samples SM clock / throttle reasons through NVML while the timed region runs."""
 
@@ -216,6 +260,10 @@ def run_b200(args):
         v, cores, sample = cpu_reference_rate(r_np, f_np, a, eta, budget_s=args.ref_budget)
         cpu = {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port", "sample": sample}
 
+    solve = None
+    if rank == 0 and world == 1 and not args.no_solve:
+        solve = gmres_mobility_solve()
+
     if rank == 0:
         # dominant kernel = mf_kernel<double,UF,wall,open,TMA>; one launch per step per rank; the
         # step's other launches (L2 flush memset, prepare_kernel) are < 0.1% of it
@@ -240,6 +288,7 @@ def run_b200(args):
             "gpu_launches": int(args.steps * plan_launches * world),
             "clocks": clocks,
             "parity_rel_err_vs_oracle": parity,
+            "gmres_mobility_solve": solve,
         }
         emit(line)
     if world > 1:
@@ -269,6 +318,7 @@ def main():
     ap.add_argument("--ref-budget", type=float, default=12.0, help="seconds of CPU work per reference sample")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-solve", action="store_true", help="skip the config-2 GMRES mobility solve")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

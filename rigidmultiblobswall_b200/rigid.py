@@ -204,3 +204,33 @@ class BlockDiagonalPreconditioner:
 def build_block_diagonal_preconditioner(bodies, r_vectors, Nblobs, eta, a, *args, **kwargs):
     """Same role as multi_bodies.build_block_diagonal_preconditioner (multi_bodies.py:752): returns the callable."""
     return BlockDiagonalPreconditioner(bodies, r_vectors, eta, a, wall=kwargs.get("wall", True))
+
+
+def solve_mobility_problem(bodies, force_torque, eta, a, tolerance=1e-8, periodic_length=None, slip=None,
+                           PC=None, restart=60, maxiter=1000, callback=None, mobility_vector_prod=None, wall=True):
+    """The `mobility` scheme of multi_bodies_utilities.py:420-540 (free rigid bodies) on the device:
+    RHS = [slip ; -force_torque] scaled to unit norm, right-preconditioned GMRES(60) on
+    linear_operator_rigid with the block-diagonal preconditioner, solution rescaled.
+    Returns (velocity [Nbodies, 6], lambda_blobs [Nblobs, 3], iterations, info)."""
+    from . import solvers
+    dev = bodies.device
+    n3 = 3 * bodies.n_blobs
+    r = bodies.get_r_vectors()
+    FT = torch.as_tensor(force_torque, dtype=torch.float64).to(dev).reshape(-1)
+    rhs = torch.zeros(n3 + 6 * bodies.n_bodies, dtype=torch.float64, device=dev)
+    if slip is not None:
+        rhs[:n3] = torch.as_tensor(slip, dtype=torch.float64).to(dev).reshape(-1)
+    rhs[n3:] = -FT
+    nrm = torch.linalg.norm(rhs)
+    if float(nrm) > 0:
+        rhs = rhs / nrm
+    if PC is None:
+        PC = BlockDiagonalPreconditioner(bodies, r, eta, a, wall=wall)
+    if mobility_vector_prod is None:
+        mobility_vector_prod = (mobility.single_wall_mobility_trans_times_force_b200 if wall
+                                else mobility.no_wall_mobility_trans_times_force_b200)
+    A = lambda v: linear_operator_rigid(v, bodies, r, eta, a, mobility_vector_prod, periodic_length=periodic_length)
+    x, info, its = solvers.gmres(A, rhs, tol=tolerance, restart=restart, maxiter=maxiter, M=PC, callback=callback)
+    if float(nrm) > 0:
+        x = x * nrm
+    return x[n3:].reshape(-1, 6), x[:n3].reshape(-1, 3), its, info
