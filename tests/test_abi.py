@@ -54,3 +54,28 @@ def test_product_path_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 txt = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in txt and "from oracle" not in txt and "mobility_oracle" not in txt, f
+
+
+def test_registration_into_a_reference_like_module():
+    """integration.register() against a stand-in with the reference's selection function shape
+    (multi_bodies.py:233-287); no GPU call is made."""
+    import types
+    from rigidmultiblobswall_b200 import integration, mobility as mb
+    ref_mb = types.SimpleNamespace(single_wall_mobility_trans_times_force_numba=lambda *a, **k: "numba")
+    mod = types.SimpleNamespace(mb=ref_mb)
+
+    def set_mobility_vector_prod(implementation, *args, **kwargs):
+        if implementation == "numba":
+            return ref_mb.single_wall_mobility_trans_times_force_numba
+    mod.set_mobility_vector_prod = set_mobility_vector_prod
+    integration.register(mod, alias_pycuda=True)
+    integration.register(mod)          # idempotent
+    assert mod.set_mobility_vector_prod("numba")() == "numba"
+    assert mod.set_mobility_vector_prod("b200") is mb.single_wall_mobility_trans_times_force_b200
+    assert mod.set_mobility_vector_prod("b200_no_wall_fp32") is mb.no_wall_mobility_trans_times_force_b200_fp32
+    assert ref_mb.single_wall_mobility_rot_times_torque_b200 is mb.single_wall_mobility_rot_times_torque_b200
+    assert ref_mb.single_wall_mobility_trans_times_torque_pycuda is mb.single_wall_mobility_trans_times_torque_b200
+    blocks = integration.roller_blocks("single_wall")
+    assert set(blocks) == {"mobility_trans_times_force", "mobility_trans_times_torque", "mobility_rot_times_force",
+                           "mobility_rot_times_torque", "mobilit_trans_times_force_torque"}
+    assert set(integration.roller_blocks("in_plane")) == {"mobility_trans_times_force", "mobility_trans_times_torque"}
