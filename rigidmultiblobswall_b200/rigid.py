@@ -201,6 +201,39 @@ class BlockDiagonalPreconditioner:
         return out
 
 
+    # ---- stochastic preconditioner (multi_bodies.py:480-618): M_b = Lc Lc^T, P = Lc^-T, P^-1 = Lc^T ... the
+    # reference stores P = inv(U) with M = U^T U (U = Lc^T): mobility_pc = P^T M P, P_inv_mult = U^T = Lc.
+    def _ensure_stoch(self):
+        if getattr(self, "L_inv", None) is None:
+            eye = torch.eye(self.m, dtype=torch.float64, device=self.bodies.device).expand(self.bodies.n_bodies, -1, -1)
+            self.L_inv = torch.linalg.solve_triangular(self.chol, eye, upper=False)
+
+    def mobility_pc(self, w, mobility_mult):
+        """y = P^T M P w with the block-diagonal P = Lc^-T; mobility_mult(v) applies the full blob mobility."""
+        self._ensure_stoch()
+        v = self._unpad((self.L_inv.transpose(1, 2) @ self._pad(w.reshape(-1)).unsqueeze(2)).squeeze(2))
+        mv = mobility_mult(v).reshape(-1)
+        return self._unpad((self.L_inv @ self._pad(mv).unsqueeze(2)).squeeze(2))
+
+    def P_inv_mult(self, w):
+        """y = P^-1 w = Lc w (maps the preconditioned Lanczos noise back, stochastic_forcing.py:256)."""
+        return self._unpad((self.chol @ self._pad(w.reshape(-1)).unsqueeze(2)).squeeze(2))
+
+
+def build_block_diagonal_preconditioners_det_stoch(bodies, r_vectors, Nblobs, eta, a, *args, **kwargs):
+    """multi_bodies.build_block_diagonal_preconditioners_det_stoch (multi_bodies.py:480): returns
+    (block_diagonal_preconditioner, mobility_pc, P_inv_mult).  kwargs: mobility_mult (callable applying the blob
+    mobility; default single-wall B200 product with kwargs['periodic_length']), wall."""
+    PC = BlockDiagonalPreconditioner(bodies, r_vectors, eta, a, wall=kwargs.get("wall", True))
+    mult = kwargs.get("mobility_mult")
+    if mult is None:
+        L = kwargs.get("periodic_length")
+        fn = (mobility.single_wall_mobility_trans_times_force_b200 if kwargs.get("wall", True)
+              else mobility.no_wall_mobility_trans_times_force_b200)
+        mult = lambda v: fn(r_vectors, v, eta, a, periodic_length=L)
+    return PC, (lambda w: PC.mobility_pc(w, mult)), PC.P_inv_mult
+
+
 def build_block_diagonal_preconditioner(bodies, r_vectors, Nblobs, eta, a, *args, **kwargs):
     """Same role as multi_bodies.build_block_diagonal_preconditioner (multi_bodies.py:752): returns the callable."""
     return BlockDiagonalPreconditioner(bodies, r_vectors, eta, a, wall=kwargs.get("wall", True))

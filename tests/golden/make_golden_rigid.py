@@ -129,6 +129,22 @@ def main():
     store.update({"lanczos/z": z, "lanczos/noise": noise, "lanczos/iterations": np.array([it_l]),
                   "lanczos/tolerance_factor": np.array([1e-10, 1.3])})
 
+    # stochastic block-diagonal preconditioner (multi_bodies.py:480-618): P^T M P and P^-1 products
+    PCd, mobility_pc, P_inv_mult = mbod.build_block_diagonal_preconditioners_det_stoch(
+        bodies, r_vectors, Nblobs, eta, a, step=0, update_PC=1, periodic_length=L)
+    w = rng.standard_normal(3 * Nblobs)
+    store["stoch/w"] = w
+    store["stoch/mobility_pc_w"] = mobility_pc(w.copy())
+    store["stoch/P_inv_w"] = P_inv_mult(w.copy())
+    store["stoch/PC_x"] = PCd(x)
+    # preconditioned Lanczos noise for the whole 12-body suspension (quaternion_integrator_multi_bodies.py:703)
+    z2 = rng.standard_normal(3 * Nblobs)
+    noise2, it2 = stochastic.stochastic_forcing_lanczos(factor=0.7, tolerance=1e-10, dim=3 * Nblobs,
+                                                        mobility_mult=mobility_pc, L_mult=P_inv_mult, z=z2)
+    print("preconditioned lanczos iterations", it2)
+    store.update({"stoch/z": z2, "stoch/noise": noise2, "stoch/iterations": np.array([it2]),
+                  "stoch/tolerance_factor": np.array([1e-10, 0.7])})
+
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "rigid_golden.npz")
     np.savez_compressed(path, **store)
     print("wrote", path, os.path.getsize(path), "bytes")

@@ -117,3 +117,22 @@ def test_lanczos_on_device(rg):
     noise, it = solvers.lanczos(factor=factor, tolerance=tol, dim=180, mobility_mult=mult, z=dev(rg["lanczos/z"]))
     assert abs(it - int(rg["lanczos/iterations"][0])) <= 1
     assert relerr(noise, rg["lanczos/noise"]) < 1e-8
+
+
+def test_stochastic_preconditioner_and_preconditioned_lanczos(rg, setup):
+    """multi_bodies.py:480-618 + quaternion_integrator_multi_bodies.py:703: P^T M P, P^-1 and the noise"""
+    from rigidmultiblobswall_b200 import solvers
+    rigid, bodies = setup
+    a, eta, _ = rg["rigid/a_eta_tol"]
+    r = bodies.get_r_vectors()
+    PC, mobility_pc, P_inv_mult = rigid.build_block_diagonal_preconditioners_det_stoch(
+        bodies, r, bodies.n_blobs, eta, a, periodic_length=np.zeros(3))
+    w = dev(rg["stoch/w"])
+    assert relerr(mobility_pc(w), rg["stoch/mobility_pc_w"]) < 1e-10
+    assert relerr(P_inv_mult(w), rg["stoch/P_inv_w"]) < 1e-12
+    assert relerr(PC(dev(rg["rigid/x"])), rg["stoch/PC_x"]) < 1e-9
+    tol, factor = rg["stoch/tolerance_factor"]
+    noise, it = solvers.lanczos(factor=factor, tolerance=tol, dim=540, mobility_mult=mobility_pc, L_mult=P_inv_mult,
+                                z=dev(rg["stoch/z"]))
+    assert abs(it - int(rg["stoch/iterations"][0])) <= 1
+    assert relerr(noise, rg["stoch/noise"]) < 1e-8
