@@ -46,6 +46,9 @@ extern "C" {
 #define RMB_SINGLE_WALL 1 /* single_wall_* : Swan-Brady wall, heights clamped to z >= a,
                              damping B applied on both sides (mobility.py:52-84)          */
 
+#define RMB_FREE_SURFACE 2 /* free_surface_mobility_trans_times_force_* (mobility.py:533,1390): RPY plus its
+                             image across a stress-free plane z = 0; RMB_UF only, no clamp, no damping    */
+
 /* precision of the pair arithmetic */
 #define RMB_FP64 0
 #define RMB_FP32 1

@@ -87,6 +87,9 @@ def mobility_product(block, wall, r_vectors, vec, eta, a, periodic_length=None,
     elif wall == "no_wall":
         assert not in_plane
         lib().rmb_oracle_block(BLOCKS[block], 0, n, _p(r), _p(v), eta, a, _p(L), b, e, _p(out))
+    elif wall == "free_surface":
+        assert not in_plane and block == "UF"
+        lib().rmb_oracle_block(BLOCKS[block], 2, n, _p(r), _p(v), eta, a, _p(L), b, e, _p(out))
     else:
         raise ValueError(wall)
     return out

@@ -266,7 +266,7 @@ static inline void wall_wt(double rx, double ry, double rz, double h, int self, 
 /*
  * One mobility block applied to a vector, for a subset of targets.
  *   block : BLK_UF / BLK_UT / BLK_WF / BLK_WT
- *   wall  : 0 = unbounded (no_wall_* functions), 1 = single wall
+ *   wall  : 0 = unbounded (no_wall_* functions), 1 = single wall, 2 = free surface (BLK_UF only)
  *   r     : n x 3 positions (already height-clamped when wall = 1)
  *   v     : n x 3 force or torque
  *   L     : periodic lengths, component <= 0 means not periodic
@@ -301,7 +301,16 @@ void rmb_oracle_block(int block, int wall, long n, const double *r, const double
             if (block == BLK_UF) free_uf(rx, ry, rz, self, &M);
             else if (block == BLK_WT) free_wt(rx, ry, rz, self, &M);
             else free_coupling(rx, ry, rz, self, &M);
-            if (wall) {
+            if (wall == 2) {
+              /* free surface (mobility_numba.py:1770-1937): add the RPY block of the image pair, evaluated at
+                 (rx, ry, (z_i+z_j)/a) WITHOUT a self branch, with the z column sign-flipped (:1918-1926) */
+              mat3 I;
+              free_uf(rx, ry, (zi + r[3 * j + 2]) * inva, 0, &I);
+              M.xx += I.xx; M.xy += I.xy; M.xz -= I.xz;
+              M.yx += I.xy; M.yy += I.yy; M.yz -= I.yz;
+              M.zx += I.xz; M.zy += I.yz; M.zz -= I.zz;
+            }
+            if (wall == 1) {
               const double Rz = (zi + r[3 * j + 2]) * inva;
               if (block == BLK_UF) wall_uf(rx, ry, Rz, r[3 * j + 2] * inva, self, &M);
               else if (block == BLK_UT) wall_ut(-rx, -ry, Rz, zi * inva, self, &M);

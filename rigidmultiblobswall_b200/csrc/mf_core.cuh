@@ -6,7 +6,7 @@
 
 namespace rmb {
 
-enum Block { UF = 0, UT = 1, WF = 2, WT = 3, UF_UT = 4 };
+enum Block { UF = 0, UT = 1, WF = 2, WT = 3, UF_UT = 4, UF_FS = 5 /* UF above a free (stress-free) surface */ };
 
 // One packed source blob in HBM / shared memory: position followed by NV
 // 3-vectors (NV = 1: force or torque; NV = 2: force and torque/a for the
@@ -108,6 +108,14 @@ RMB_HD void pair_apply(const PairGeom<T>& g, T ht, const T* v, bool any_near, T 
   if (BLOCK == UF || BLOCK == UF_UT) pair_uf<T, WALL>(g, ht, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
   if (BLOCK == WF) pair_wf<T, WALL>(g, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
   if (BLOCK == WT) pair_wt<T, WALL>(g, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
+  if (BLOCK == UF_FS) {
+    // free surface (mobility_numba.py:1770-1937): RPY(r) f + RPY(R) f', R = (rx, ry, z_i+z_j), f' = (fx, fy, -fz)
+    // (the image block enters with the sign pattern [+ + -; + + -; + + -] on its columns, :1918-1926)
+    pair_uf<T, false>(g, ht, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
+    PairGeom<T> gi = g;
+    gi.rz = g.Rz;
+    pair_uf<T, false>(gi, ht, v[0], v[1], -v[2], true, RMB_FMA(g.Rz, g.Rz, rxy2), rxy2, ux, uy, uz);
+  }
   if (BLOCK == UT || BLOCK == UF_UT) {
     PairGeom<T> gt = g;
     gt.h = ht;
@@ -125,6 +133,13 @@ RMB_HD void self_apply(T h, const T* v, T& ux, T& uy, T& uz)
   if (BLOCK == WF && WALL) self_wf<T>(h, v[0], v[1], ux, uy);
   if (BLOCK == WT) self_wt<T, WALL>(h, v[0], v[1], v[2], ux, uy, uz);
   if (BLOCK == UF_UT && WALL) self_ut<T>(h, v[3], v[4], ux, uy);
+  if (BLOCK == UF_FS) {
+    // i == j: 4/3 f plus the blob's own image at distance 2h, which is an ordinary (far or near) pair
+    self_uf<T, false>(h, v[0], v[1], v[2], ux, uy, uz);
+    PairGeom<T> gi;
+    gi.rx = T(0); gi.ry = T(0); gi.rz = h + h; gi.Rz = gi.rz; gi.h = h;
+    pair_uf<T, false>(gi, h, v[0], v[1], -v[2], true, gi.rz * gi.rz, T(0), ux, uy, uz);
+  }
 }
 
 // Normalisation 1/(8 pi eta a^k), k = 1 (UF, fused), 2 (UT, WF), 3 (WT).

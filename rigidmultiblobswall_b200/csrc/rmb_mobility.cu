@@ -392,7 +392,7 @@ int launch(const Call& c)
   const long n_pad = (long)p.n_tiles * TILE;
   const int in_plane = (c.flags & RMB_IN_PLANE) ? 1 : 0;
   prepare_kernel<T, NV><<<(unsigned)((n_pad + 255) / 256), 256, 0, c.stream>>>(
-      c.n_src, n_pad, c.r, c.va, c.vb, c.a, WALL ? 1 : 0, PERIODIC ? 0 : 1, in_plane, rec, damp);
+      c.n_src, n_pad, c.r, c.va, c.vb, c.a, (WALL && BLOCK != UF_FS) ? 1 : 0, PERIODIC ? 0 : 1, in_plane, rec, damp);
 
   MfArgs<T, NV> A;
   A.src = rec;
@@ -437,6 +437,7 @@ int launch_block(const Call& c, bool per)
     case RMB_WF: return launch_wp<T, WF>(c, per);
     case RMB_WT: return launch_wp<T, WT>(c, per);
     case RMB_UF_UT: return launch_wp<T, UF_UT>(c, per);
+    case UF_FS: return per ? launch<T, UF_FS, true, true>(c) : launch<T, UF_FS, true, false>(c);
   }
   return fail(RMB_E_ARG, "unknown block");
 }
@@ -479,7 +480,9 @@ int rmb_mobility_product(int block, int wall, int precision, int flags, long n_t
                          size_t workspace_bytes, void* stream)
 {
   if (block < 0 || block > RMB_UF_UT) return fail(RMB_E_ARG, "block must be RMB_UF..RMB_UF_UT");
-  if (wall != RMB_NO_WALL && wall != RMB_SINGLE_WALL) return fail(RMB_E_ARG, "wall must be 0 or 1");
+  if (wall != RMB_NO_WALL && wall != RMB_SINGLE_WALL && wall != RMB_FREE_SURFACE)
+    return fail(RMB_E_ARG, "wall must be RMB_NO_WALL, RMB_SINGLE_WALL or RMB_FREE_SURFACE");
+  if (wall == RMB_FREE_SURFACE && block != RMB_UF) return fail(RMB_E_ARG, "RMB_FREE_SURFACE exists for RMB_UF only");
   if (precision != RMB_FP64 && precision != RMB_FP32) return fail(RMB_E_ARG, "precision must be 0 or 1");
   if (n_targets < 0 || n_sources < 0 || target_offset < 0 || target_offset + n_targets > n_sources)
     return fail(RMB_E_ARG, "target range must lie inside [0, n_sources)");
@@ -489,7 +492,7 @@ int rmb_mobility_product(int block, int wall, int precision, int flags, long n_t
   if (!(a > 0) || !(eta > 0)) return fail(RMB_E_ARG, "a and eta must be positive");
   if ((reinterpret_cast<uintptr_t>(workspace) & 15) != 0) return fail(RMB_E_ARG, "workspace must be 16-byte aligned");
   Call c;
-  c.block = block; c.wall = wall; c.precision = precision; c.flags = flags;
+  c.block = (wall == RMB_FREE_SURFACE) ? (int)UF_FS : block; c.wall = wall; c.precision = precision; c.flags = flags;
   c.n_tgt = n_targets; c.n_src = n_sources; c.tgt_off = target_offset;
   c.r = r_sources; c.va = vec_a; c.vb = vec_b; c.eta = eta; c.a = a;
   for (int d = 0; d < 3; d++) c.L[d] = L ? L[d] : 0.0;

@@ -29,7 +29,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import FP32, FP64, IN_PLANE, NO_TMA, NO_WALL, SINGLE_WALL, UF, UF_UT, UT, WF, WT  # noqa: F401
+from ._lib import FP32, FP64, FREE_SURFACE, IN_PLANE, NO_TMA, NO_WALL, SINGLE_WALL, UF, UF_UT, UT, WF, WT  # noqa: F401
 
 _workspaces = {}
 default_flags = int(os.environ.get("RMB_FLAGS", "0"))  # OR-ed into every call (debug: RMB_FLAGS=2 -> RMB_NO_TMA)
@@ -120,6 +120,7 @@ _TABLE = [
     ("single_wall_mobility_rot_times_force", WF, SINGLE_WALL, 0, ":1273; :300"),
     ("no_wall_mobility_rot_times_torque", WT, NO_WALL, 0, ":1301; :370"),
     ("single_wall_mobility_rot_times_torque", WT, SINGLE_WALL, 0, ":1316; :342"),
+    ("free_surface_mobility_trans_times_force", UF, FREE_SURFACE, 0, ":1390; :533"),
 ]
 
 __all__ = ["mobility_product"]

@@ -115,6 +115,16 @@ def main():
     print("numba vs dense single_wall_fluid_mobility:", err)
     assert err < 1e-13
 
+    # free surface (mobility.py:1390 -> mobility_numba.py:1770): no clamp, all z > 0
+    for cname in ("dense", "dilute"):
+        r, a, eta = cl[cname]
+        v = store[f"{cname}/v"]
+        for lname in ("open", "xy"):
+            L = store[f"{cname}/L_{lname}"]
+            key = f"{cname}/{lname}/free_surface/UF"
+            store[key] = np.asarray(mb.free_surface_mobility_trans_times_force_numba(r, v, eta, a, periodic_length=L))
+            cases.append(key)
+
     store["cases"] = np.array(cases)
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "mf_golden.npz")
     np.savez_compressed(path, **store)

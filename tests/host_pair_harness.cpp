@@ -21,7 +21,7 @@ static void run(long n, const double* r, const double* va, const double* vb, dou
   const double s = PERIODIC ? 1.0 : inva;
   for (long j = 0; j < n; j++) {
     double z = r[3 * j + 2], B = 1.0;
-    if (WALL) { B = (z < a) ? z / a : 1.0; z = (z <= a) ? a : z; }
+    if (WALL && BLOCK != UF_FS) { B = (z < a) ? z / a : 1.0; z = (z <= a) ? a : z; }
     damp[j] = B;
     rec[j].x = T(r[3 * j] * s); rec[j].y = T(r[3 * j + 1] * s); rec[j].z = T(z * s);
     for (int c = 0; c < 3; c++) rec[j].v[c] = T(B * va[3 * j + c]);
@@ -78,6 +78,7 @@ static void run_b(int block, int wall, bool per, long n, const double* r, const 
     case WF: run_wp<T, WF>(wall, per, n, r, va, vb, eta, a, L, in_plane, out); break;
     case WT: run_wp<T, WT>(wall, per, n, r, va, vb, eta, a, L, in_plane, out); break;
     case UF_UT: run_wp<T, UF_UT>(wall, per, n, r, va, vb, eta, a, L, in_plane, out); break;
+    case UF_FS: run_wp<T, UF_FS>(1, per, n, r, va, vb, eta, a, L, in_plane, out); break;
   }
 }
 

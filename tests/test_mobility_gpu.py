@@ -38,7 +38,7 @@ def _run(mb, case, golden, precision, flags=0):
     a, eta = golden[f"{cloud}/a_eta"]
     L = golden[f"{cloud}/L_{lname}"]
     fl = flags | (mb.IN_PLANE if wall == "in_plane" else 0)
-    w = mb.NO_WALL if wall == "no_wall" else mb.SINGLE_WALL
+    w = {"no_wall": mb.NO_WALL, "free_surface": mb.FREE_SURFACE}.get(wall, mb.SINGLE_WALL)
     return mb.mobility_product(BLOCK_ID[blk], w, r, v, eta, a, periodic_length=L, precision=precision, flags=fl)
 
 

@@ -10,7 +10,7 @@ import pytest
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
-BLOCKS = {"UF": 0, "UT": 1, "WF": 2, "WT": 3, "UF_UT": 4}
+BLOCKS = {"UF": 0, "UT": 1, "WF": 2, "WT": 3, "UF_UT": 4, "UF_FS": 5}
 
 
 @pytest.fixture(scope="module")
@@ -50,7 +50,8 @@ def test_algebra_fp64(golden, harness, case):
     r, v = golden[f"{cloud}/r"], golden[f"{cloud}/v"]
     a, eta = golden[f"{cloud}/a_eta"]
     L = golden[f"{cloud}/L_{lname}"]
-    out = harness(blk, wall != "no_wall", r, v, eta, a, L, in_plane=(wall == "in_plane"))
+    out = harness("UF_FS" if wall == "free_surface" else blk, wall != "no_wall", r, v, eta, a, L,
+                  in_plane=(wall == "in_plane"))
     assert relerr(out, golden[case]) < 1e-12   # BASELINE.json: fp64 parity bar
 
 
@@ -60,7 +61,8 @@ def test_algebra_fp32(golden, harness, case):
     r, v = golden[f"{cloud}/r"], golden[f"{cloud}/v"]
     a, eta = golden[f"{cloud}/a_eta"]
     L = golden[f"{cloud}/L_{lname}"]
-    out = harness(blk, wall != "no_wall", r, v, eta, a, L, fp32=True, in_plane=(wall == "in_plane"))
+    out = harness("UF_FS" if wall == "free_surface" else blk, wall != "no_wall", r, v, eta, a, L, fp32=True,
+                  in_plane=(wall == "in_plane"))
     assert relerr(out, golden[case]) < 1e-5    # BASELINE.json: fp32 parity bar
 
 
