@@ -57,6 +57,10 @@ def lib():
         _lib.rmb_oracle_uf_wall_fast.argtypes = [ctypes.c_long, dp, dp, ctypes.c_double, ctypes.c_double,
                                                  ctypes.c_long, ctypes.c_long, dp]
         _lib.rmb_oracle_threads.restype = ctypes.c_int
+        _lib.rmb_oracle_source_target.argtypes = [ctypes.c_int, ctypes.c_long, ctypes.c_long, dp, dp, dp, dp, dp,
+                                                  ctypes.c_double, dp, dp]
+        _lib.rmb_oracle_source_target_wall_wrap.argtypes = [ctypes.c_long, ctypes.c_long, dp, dp, dp, dp, dp,
+                                                            ctypes.c_double, dp, dp]
     return _lib
 
 
@@ -103,4 +107,27 @@ def uf_wall_fast(r_vectors, force, eta, a, targets=None):
     b, e = (0, n) if targets is None else targets
     out = np.empty(3 * (e - b))
     lib().rmb_oracle_uf_wall_fast(n, _p(r), _p(v), eta, a, b, e, _p(out))
+    return out
+
+
+def source_target(wall, source, target, force, radius_source, radius_target, eta, periodic_length=None):
+    """Mirrors mobility.py's `<wall>_mobility_trans_times_force_source_target_numba(source, target, force,
+    radius_source, radius_target, eta, periodic_length=L)` (:551, :588, :1407); wall in
+    {'single_wall','no_wall','free_surface'}.  The single-wall form includes the per-radius clamp and damping."""
+    src = np.ascontiguousarray(np.asarray(source, dtype=np.float64).reshape(-1, 3))
+    trg = np.ascontiguousarray(np.asarray(target, dtype=np.float64).reshape(-1, 3))
+    f = np.ascontiguousarray(np.asarray(force, dtype=np.float64).reshape(-1, 3))
+    rs = np.ascontiguousarray(radius_source, dtype=np.float64)
+    rt = np.ascontiguousarray(radius_target, dtype=np.float64)
+    L = np.zeros(3) if periodic_length is None else np.ascontiguousarray(periodic_length, dtype=np.float64)
+    ns, nt = src.shape[0], trg.shape[0]
+    assert f.shape[0] == ns and rs.size == ns and rt.size == nt
+    out = np.zeros(3 * nt)
+    if wall == "single_wall":
+        lib().rmb_oracle_source_target_wall_wrap(nt, ns, _p(trg), _p(src), _p(f), _p(rt), _p(rs), eta, _p(L), _p(out))
+    elif wall in ("no_wall", "free_surface"):
+        lib().rmb_oracle_source_target(0 if wall == "no_wall" else 2, nt, ns, _p(trg), _p(src), _p(f), _p(rt), _p(rs),
+                                       eta, _p(L), _p(out))
+    else:
+        raise ValueError(wall)
     return out

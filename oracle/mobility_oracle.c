@@ -452,3 +452,173 @@ void rmb_oracle_uf_wall_fast(long n, const double *r, const double *v, double et
   }
   free(X);
 }
+
+/* ------------------------------------------------------------------------
+ * Source-target kernels with per-blob radii.
+ *   mobility_trans_times_force_source_target_numba ........ mobility_numba.py:1480-1658
+ *   free_surface_mobility_trans_times_force_source_target_numba ... :1941-2092
+ * Restated expression by expression; there is no self branch (the r = 0 pair
+ * falls in the "complete overlap" case, :1563-1566).
+ * ---------------------------------------------------------------------- */
+
+/* Zuk et al. (2014) RPY coefficients for unequal radii (:1552-1566) */
+static inline void rpy_radii_coeff(double r2, double a, double b, double *C1, double *C2)
+{
+  const double fourOverThree = 4.0 / 3.0;
+  const double r = sqrt(r2);
+  if (r > (a + b)) {
+    const double a2 = a * a, b2 = b * b;
+    *C1 = (1 + (b2 + a2) / (3 * r2)) / r;
+    *C2 = ((1 - (b2 + a2) / r2) / r2) / r;
+  } else if (r > fabs(b - a)) {
+    const double r3 = r2 * r;
+    const double bma2 = (b - a) * (b - a);
+    *C1 = ((16 * (b + a) * r3 - (bma2 + 3 * r2) * (bma2 + 3 * r2)) / (32 * r3)) * fourOverThree / (b * a);
+    *C2 = ((3 * (bma2 - r2) * (bma2 - r2) / (32 * r3)) / r2) * fourOverThree / (b * a);
+  } else {
+    const double largest_radius = a > b ? a : b;
+    *C1 = fourOverThree / largest_radius;
+    *C2 = 0;
+  }
+}
+
+/*
+ * wall : 0 = unbounded, 1 = no-slip wall correction (:1581-1647), 2 = free surface (:2040-2081).
+ * No clamp / damping here: that is the python wrapper (mobility.py:551-585), restated in
+ * rmb_oracle_source_target_wall_wrap below.
+ */
+void rmb_oracle_source_target(int wall, long n_trg, long n_src, const double *target, const double *source,
+                              const double *force, const double *radius_target, const double *radius_source,
+                              double eta, const double *L, double *out)
+{
+  const double norm_fact_f = 1.0 / (8.0 * M_PI * eta);
+  const int px = L[0] > 0, py = L[1] > 0, pz = L[2] > 0;
+#pragma omp parallel for schedule(static)
+  for (long i = 0; i < n_trg; i++) {
+    const double rxi = target[3 * i], ryi = target[3 * i + 1], rzi = target[3 * i + 2];
+    const double a = radius_target[i];
+    double ux = 0, uy = 0, uz = 0;
+    for (int bx = -px; bx <= px; bx++)
+      for (int by = -py; by <= py; by++)
+        for (int bz = -pz; bz <= pz; bz++)
+          for (long j = 0; j < n_src; j++) {
+            const double b = radius_source[j];
+            double rx = wrap_shift(rxi - source[3 * j], L[0], bx);
+            double ry = wrap_shift(ryi - source[3 * j + 1], L[1], by);
+            double rz = wrap_shift(rzi - source[3 * j + 2], L[2], bz);
+            double r2 = rx * rx + ry * ry + rz * rz;
+            double C1, C2;
+            rpy_radii_coeff(r2, a, b, &C1, &C2);
+            double Mxx = C1 + C2 * rx * rx, Mxy = C2 * rx * ry, Mxz = C2 * rx * rz;
+            double Myy = C1 + C2 * ry * ry, Myz = C2 * ry * rz, Mzz = C1 + C2 * rz * rz;
+            double Myx = Mxy, Mzx = Mxz, Mzy = Myz;
+            if (wall == 2) {
+              rz = rzi + source[3 * j + 2];
+              r2 = rx * rx + ry * ry + rz * rz;
+              rpy_radii_coeff(r2, a, b, &C1, &C2);
+              const double Ixx = C1 + C2 * rx * rx, Ixy = C2 * rx * ry, Ixz = C2 * rx * rz;
+              const double Iyy = C1 + C2 * ry * ry, Iyz = C2 * ry * rz, Izz = C1 + C2 * rz * rz;
+              Mxx = Mxx + Ixx; Mxy = Mxy + Ixy; Mxz = Mxz - Ixz;
+              Myx = Myx + Ixy; Myy = Myy + Iyy; Myz = Myz - Iyz;
+              Mzx = Mzx + Ixz; Mzy = Mzy + Iyz; Mzz = Mzz - Izz;
+            }
+            if (wall == 1) {
+              const double y3 = source[3 * j + 2];
+              const double x3 = rzi;
+              rz = rzi + source[3 * j + 2];
+              r2 = rx * rx + ry * ry + rz * rz;
+              const double r = sqrt(r2);
+              const double a2 = a * a, b2 = b * b;
+              const double r3 = r2 * r, r5 = r3 * r2, r7 = r5 * r2, r9 = r7 * r2;
+
+              Mxx -= ((1 + (b2 + a2) / (3.0 * r2)) + (1 - (b2 + a2) / r2) * rx * rx / r2) / r;
+              Mxy -= ((1 - (b2 + a2) / r2) * rx * ry / r2) / r;
+              Mxz += ((1 - (b2 + a2) / r2) * rx * rz / r2) / r;
+              Myx -= ((1 - (b2 + a2) / r2) * ry * rx / r2) / r;
+              Myy -= ((1 + (b2 + a2) / (3.0 * r2)) + (1 - (b2 + a2) / r2) * ry * ry / r2) / r;
+              Myz += ((1 - (b2 + a2) / r2) * ry * rz / r2) / r;
+              Mzx -= ((1 - (b2 + a2) / r2) * rz * rx / r2) / r;
+              Mzy -= ((1 - (b2 + a2) / r2) * rz * ry / r2) / r;
+              Mzz += ((1 + (b2 + a2) / (3.0 * r2)) + (1 - (b2 + a2) / r2) * rz * rz / r2) / r;
+
+              Mxx -= 2 * (x3 * y3 * (1.0 / r3 - 3 * rx * rx / r5));
+              Mxy -= 2 * (x3 * y3 * (-3 * rx * ry / r5));
+              Mxz += 2 * (-rx * x3 / r3 + x3 * y3 * (-3 * rx * rz / r5));
+              Myx -= 2 * (x3 * y3 * (-3 * ry * rx / r5));
+              Myy -= 2 * (x3 * y3 * (1.0 / r3 - 3 * ry * ry / r5));
+              Myz += 2 * (-ry * x3 / r3 + x3 * y3 * (-3 * ry * rz / r5));
+              Mzx -= 2 * (-y3 * rx / r3 + x3 * y3 * (-3 * rz * rx / r5));
+              Mzy -= 2 * (-y3 * ry / r3 + x3 * y3 * (-3 * rz * ry / r5));
+              Mzz += 2 * (-1.0 / r - rz * x3 / r3 - y3 * rz / r3 + x3 * y3 * (1.0 / r3 - 3 * rz * rz / r5));
+
+              Mxx -= (2 * a2 / 3.0) * (-y3 * (3 * rz / r5 - 15 * rz * rx * rx / r7));
+              Mxy -= (2 * a2 / 3.0) * (-y3 * (-15 * rz * rx * ry / r7));
+              Mxz += (2 * a2 / 3.0) * (3 * rx * rz / r5 - y3 * (3 * rx / r5 - 15 * rz * rx * rz / r7));
+              Myx -= (2 * a2 / 3.0) * (-y3 * (-15 * rz * ry * rx / r7));
+              Myy -= (2 * a2 / 3.0) * (-y3 * (3 * rz / r5 - 15 * rz * ry * ry / r7));
+              Myz += (2 * a2 / 3.0) * (3 * ry * rz / r5 - y3 * (3 * ry / r5 - 15 * rz * ry * rz / r7));
+              Mzx -= (2 * a2 / 3.0) * (-y3 * (3 * rx / r5 - 15 * rz * rz * rx / r7));
+              Mzy -= (2 * a2 / 3.0) * (-y3 * (3 * ry / r5 - 15 * rz * rz * ry / r7));
+              Mzz += (2 * a2 / 3.0) * (-1.0 / r3 + 3 * rz * rz / r5 - y3 * (3 * rz / r5 + 3 * rz / r5 + 3 * rz / r5 - 15 * rz * rz * rz / r7));
+
+              Mxx -= (2 * b2 / 3.0) * (-x3 * (3 * rz / r5 - 15 * rz * rx * rx / r7));
+              Mxy -= (2 * b2 / 3.0) * (-x3 * (-15 * rz * rx * ry / r7));
+              Mxz += (2 * b2 / 3.0) * (-x3 * (3 * rx / r5 - 15 * rz * rx * rz / r7));
+              Myx -= (2 * b2 / 3.0) * (-x3 * (-15 * rz * ry * rx / r7));
+              Myy -= (2 * b2 / 3.0) * (-x3 * (3 * rz / r5 - 15 * rz * ry * ry / r7));
+              Myz += (2 * b2 / 3.0) * (-x3 * (3 * ry / r5 - 15 * rz * ry * rz / r7));
+              Mzx -= (2 * b2 / 3.0) * (3 * rz * rx / r5 - x3 * (3 * rx / r5 - 15 * rz * rz * rx / r7));
+              Mzy -= (2 * b2 / 3.0) * (3 * rz * ry / r5 - x3 * (3 * ry / r5 - 15 * rz * rz * ry / r7));
+              Mzz += (2 * b2 / 3.0) * (-1.0 / r3 + 3 * rz * rz / r5 - x3 * (3 * rz / r5 + 3 * rz / r5 + 3 * rz / r5 - 15 * rz * rz * rz / r7));
+
+              Mxx -= (2 * b2 * a2 / 3.0) * (-1.0 / r5 + 5 * rz * rz / r7 + 5 * rx * rx / r7 - 35 * rz * rz * rx * rx / r9);
+              Mxy -= (2 * b2 * a2 / 3.0) * (5 * rx * ry / r7 - 35 * rz * rz * rx * ry / r9);
+              Mxz += (2 * b2 * a2 / 3.0) * (5 * rx * rz / r7 + 5 * rx * rz / r7 + 5 * rx * rz / r7 - 35 * rz * rz * rx * rz / r9);
+              Myx -= (2 * b2 * a2 / 3.0) * (5 * ry * rx / r7 - 35 * rz * rz * ry * rx / r9);
+              Myy -= (2 * b2 * a2 / 3.0) * (-1.0 / r5 + 5 * rz * rz / r7 + 5 * ry * ry / r7 - 35 * rz * rz * ry * ry / r9);
+              Myz += (2 * b2 * a2 / 3.0) * (5 * ry * rz / r7 + 5 * ry * rz / r7 + 5 * ry * rz / r7 - 35 * rz * rz * rz * ry / r9);
+              Mzx -= (2 * b2 * a2 / 3.0) * (5 * rz * rx / r7 + 5 * rz * rx / r7 + 5 * rz * rx / r7 - 35 * rz * rz * rz * rx / r9);
+              Mzy -= (2 * b2 * a2 / 3.0) * (5 * rz * ry / r7 + 5 * rz * ry / r7 + 5 * rz * ry / r7 - 35 * rz * rz * rz * ry / r9);
+              Mzz += (2 * b2 * a2 / 3.0) * (-1.0 / r5 + 5 * rz * rz / r7 - 1.0 / r5 + 5 * rz * rz / r7 - 1.0 / r5 + 5 * rz * rz / r7 + 5 * rz * rz / r7 + 5 * rz * rz / r7 + 5 * rz * rz / r7 - 35 * rz * rz * rz * rz / r9);
+            }
+            const double fx = force[3 * j], fy = force[3 * j + 1], fz = force[3 * j + 2];
+            ux += (Mxx * fx + Mxy * fy + Mxz * fz) * norm_fact_f;
+            uy += (Myx * fx + Myy * fy + Myz * fz) * norm_fact_f;
+            uz += (Mzx * fx + Mzy * fy + Mzz * fz) * norm_fact_f;
+          }
+    out[3 * i] = ux; out[3 * i + 1] = uy; out[3 * i + 2] = uz;
+  }
+}
+
+/*
+ * mobility.py:551-585 (single_wall_mobility_trans_times_force_source_target_numba):
+ * heights clamped to the blob's own radius (shift_heights_different_radius, :87-99),
+ * B_ii = z_i / radius_i where z_i < radius_i (damping_matrix_B_different_radius, :102-119),
+ * result = B_target * M(y_eff, x_eff) * (B_source * force).
+ */
+void rmb_oracle_source_target_wall_wrap(long n_trg, long n_src, const double *target, const double *source,
+                                        const double *force, const double *radius_target,
+                                        const double *radius_source, double eta, const double *L, double *out)
+{
+  double *x = (double *)malloc(sizeof(double) * 3 * (n_trg > 0 ? n_trg : 1));
+  double *y = (double *)malloc(sizeof(double) * 3 * (n_src > 0 ? n_src : 1));
+  double *f = (double *)malloc(sizeof(double) * 3 * (n_src > 0 ? n_src : 1));
+  for (long k = 0; k < n_trg; k++) {
+    x[3 * k] = target[3 * k]; x[3 * k + 1] = target[3 * k + 1];
+    x[3 * k + 2] = target[3 * k + 2] > radius_target[k] ? target[3 * k + 2] : radius_target[k];
+  }
+  for (long k = 0; k < n_src; k++) {
+    const double z = source[3 * k + 2];
+    const double B = z < radius_source[k] ? z / radius_source[k] : 1.0;
+    y[3 * k] = source[3 * k]; y[3 * k + 1] = source[3 * k + 1];
+    y[3 * k + 2] = z > radius_source[k] ? z : radius_source[k];
+    f[3 * k] = B * force[3 * k]; f[3 * k + 1] = B * force[3 * k + 1]; f[3 * k + 2] = B * force[3 * k + 2];
+  }
+  rmb_oracle_source_target(1, n_trg, n_src, x, y, f, radius_target, radius_source, eta, L, out);
+  for (long k = 0; k < n_trg; k++) {
+    const double z = target[3 * k + 2];
+    const double B = z < radius_target[k] ? z / radius_target[k] : 1.0;
+    out[3 * k] *= B; out[3 * k + 1] *= B; out[3 * k + 2] *= B;
+  }
+  free(x); free(y); free(f);
+}

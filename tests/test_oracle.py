@@ -46,3 +46,26 @@ def test_vectorised_timing_variant_matches_reference_numba(golden, cloud):
     assert relerr(out, golden[f"{cloud}/open/single_wall/UF"]) < 1e-13
     part = oracle.uf_wall_fast(r, v, eta, a, targets=(5, 40))
     assert np.array_equal(part, out[15:120])
+
+
+# ---- source-target kernels with per-blob radii (mobility_numba.py:1480, :1941) ----
+def _st():
+    import os
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "st_golden.npz"))
+
+
+def _st_cases():
+    return [str(c) for c in _st()["cases"]]
+
+
+@pytest.mark.parametrize("case", _st_cases())
+def test_oracle_source_target_matches_reference_numba(case):
+    g = _st()
+    name, lname, wall = case.split("/")
+    src, trg, f = g[f"{name}/source"], g[f"{name}/target"], g[f"{name}/force"]
+    rs, rt, eta, L = g[f"{name}/radius_source"], g[f"{name}/radius_target"], float(g[f"{name}/eta"]), g[f"{name}/L_{lname}"]
+    if wall == "radii_single_wall":
+        out = oracle.source_target("single_wall", src, src, f, rs, rs, eta, L)
+    else:
+        out = oracle.source_target(wall, src, trg, f, rs, rt, eta, L)
+    assert relerr(out, g[case]) < 1e-13
