@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define RMB_VERSION 100 /* 0.1.0 */
+#define RMB_VERSION 101 /* 0.1.1 */
 
 /* block: which mobility block is applied (mobility.py naming in comments) */
 #define RMB_UF 0    /* *_mobility_trans_times_force        (mobility.py:222,288,1119,1132) */
@@ -98,6 +98,33 @@ int rmb_mobility_product(int block, int wall, int precision, int flags,
                          const double *r_sources, const double *vec_a, const double *vec_b,
                          double eta, double a, const double *L,
                          double *out, void *workspace, size_t workspace_bytes, void *stream);
+
+/*
+ * Source-target UF product with per-blob radii: the flow at n_targets blobs
+ * created by forces on n_sources other (or the same) blobs,
+ *     out = B_t * M(x_eff, y_eff; radius_t, radius_s) * (B_s * force)      (wall = RMB_SINGLE_WALL)
+ *     out = M(x, y; radius_t, radius_s) * force                            (RMB_NO_WALL, RMB_FREE_SURFACE)
+ * in units of 1/(8 pi eta).  Replaces
+ *   mobility.{single_wall,no_wall,free_surface}_mobility_trans_times_force_source_target_{numba,pycuda}
+ *   (mobility/mobility.py:494, :551, :588, :1407 -> mobility_numba.py:1480-1658, :1941-2092;
+ *   mobility_pycuda.py:1394) and mobility.mobility_radii_trans_times_force (:1369, sources == targets).
+ * RPY for unequal radii (far / partial overlap / complete overlap, the latter also covering a target that
+ * coincides with a source: there is no self branch); the wall form clamps every height to the blob's own radius
+ * and damps with B_ii = z_i / radius_i where z_i < radius_i (mobility.py:87-119); pseudo-periodic image boxes
+ * as in rmb_mobility_product.
+ *
+ *   r_targets       device, 3*n_targets     radius_targets  device, n_targets
+ *   r_sources       device, 3*n_sources     radius_sources  device, n_sources
+ *   force           device, 3*n_sources     out             device, 3*n_targets
+ *   L               host, 3 doubles or NULL
+ *   workspace       device, >= rmb_source_target_workspace_bytes(...) bytes, 16-byte aligned
+ */
+size_t rmb_source_target_workspace_bytes(int precision, long n_targets, long n_sources, const double *L);
+int rmb_mobility_source_target(int wall, int precision, int flags, long n_targets, long n_sources,
+                               const double *r_targets, const double *r_sources, const double *force,
+                               const double *radius_targets, const double *radius_sources, double eta,
+                               const double *L, double *out, void *workspace, size_t workspace_bytes,
+                               void *stream);
 
 /*
  * FP64 (precision = RMB_FP64) or FP32 FMA-pipe peak probe: runs `iters`

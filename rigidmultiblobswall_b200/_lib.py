@@ -39,6 +39,13 @@ def load():
                                          ctypes.c_long, ctypes.c_long, ctypes.c_long,
                                          c_dp, c_dp, c_dp, ctypes.c_double, ctypes.c_double,
                                          ctypes.POINTER(ctypes.c_double), c_dp, c_dp, ctypes.c_size_t, c_dp]
+    lib.rmb_source_target_workspace_bytes.restype = ctypes.c_size_t
+    lib.rmb_source_target_workspace_bytes.argtypes = [ctypes.c_int, ctypes.c_long, ctypes.c_long,
+                                                      ctypes.POINTER(ctypes.c_double)]
+    lib.rmb_mobility_source_target.restype = ctypes.c_int
+    lib.rmb_mobility_source_target.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_long, ctypes.c_long,
+                                               c_dp, c_dp, c_dp, c_dp, c_dp, ctypes.c_double,
+                                               ctypes.POINTER(ctypes.c_double), c_dp, c_dp, ctypes.c_size_t, c_dp]
     lib.rmb_fma_peak.restype = ctypes.c_int
     lib.rmb_fma_peak.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double),
                                  ctypes.POINTER(ctypes.c_double)]

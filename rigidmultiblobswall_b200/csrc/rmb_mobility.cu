@@ -18,6 +18,7 @@
 
 #include "../../include/rmb_mobility.h"
 #include "mf_core.cuh"
+#include "tile_pipe.cuh"
 
 using namespace rmb;
 
@@ -56,65 +57,6 @@ int fail_cuda(cudaError_t e, const char* where)
 {
   snprintf(g_err, sizeof(g_err), "%s: %s", where, cudaGetErrorString(e));
   return (int)e;
-}
-
-// ------------------------------------------------------------ PTX helpers --
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
-{
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
-{
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
-{
-  uint32_t done;
-  do {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(smem_u32(bar)), "r"(parity)
-        : "memory");
-  } while (!done);
-}
-// 1-D bulk async copy global -> shared (TMA engine, SASS UBLKCP), completion
-// counted in bytes on an mbarrier.  dst/src 16-byte aligned, bytes % 16 == 0.
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
-{
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                   smem_u32(dst)),
-               "l"(src), "r"(bytes), "r"(smem_u32(bar))
-               : "memory");
-}
-__device__ __forceinline__ void fence_barrier_init()
-{
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-
-// 16-byte shared-memory loads of one record (all lanes read the same address:
-// a broadcast, one wavefront each).
-template <int W>
-__device__ __forceinline__ void load_rec(const double* p, double (&w)[W])
-{
-#pragma unroll
-  for (int k = 0; k < W / 2; k++) {
-    const double2 v = reinterpret_cast<const double2*>(p)[k];
-    w[2 * k] = v.x; w[2 * k + 1] = v.y;
-  }
-}
-template <int W>
-__device__ __forceinline__ void load_rec(const float* p, float (&w)[W])
-{
-#pragma unroll
-  for (int k = 0; k < W / 4; k++) {
-    const float4 v = reinterpret_cast<const float4*>(p)[k];
-    w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
-  }
 }
 
 // ---------------------------------------------------------------- prepare --
@@ -358,10 +300,11 @@ int make_plan(int block, int precision, long n_tgt, long n_src, const double* L,
   // fewer than RMB_WAVES waves of resident CTAs (tail effect / idle SMs).  A
   // split keeps >= 4 tiles so the prologue stays amortised.
   const int resident = sms * (768 / TPB);
-  int split = (RMB_WAVES * resident + p.tgt_blocks - 1) / p.tgt_blocks;
+  int split = (RMB_WAVES * resident + p.tgt_blocks - 1) / (p.tgt_blocks > 0 ? p.tgt_blocks : 1);
   if (split > p.n_vt / 4) split = p.n_vt / 4;
   if (split < 1) split = 1;
   p.vt_per_split = (p.n_vt + split - 1) / split;
+  if (p.vt_per_split < 1) p.vt_per_split = 1;   // empty source set
   p.n_split = (p.n_vt + p.vt_per_split - 1) / p.vt_per_split;
   p.rec_bytes = (size_t)p.n_tiles * TILE * W * word;
   p.off_damp = align_up(p.rec_bytes, 256);
@@ -458,6 +401,11 @@ __global__ void fma_peak_kernel(int iters, T* sink)
 }
 
 }  // namespace
+
+namespace rmb {
+// rmb_last_error() is shared by every translation unit of the library
+void set_last_error(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg); }
+}  // namespace rmb
 
 // ------------------------------------------------------------------ C ABI --
 extern "C" {

@@ -92,6 +92,50 @@ def mobility_product(block, wall, r_vectors, vec, eta, a, periodic_length=None, 
         return out.cpu().numpy() if host_in else out
 
 
+def mobility_source_target(wall, source, target, force, radius_source, radius_target, eta, periodic_length=None,
+                           precision=FP64, flags=0, out=None):
+    """Flow at `target` created by `force` on `source`, blobs with individual radii (argument order of
+    mobility.py:551: source first).  The wall form clamps heights to each blob's radius and damps (mobility.py:87-119)."""
+    lib = _lib.load()
+    host_in = not isinstance(source, torch.Tensor)
+    dev = _device(None if host_in else source.device)
+    ns = (source.numel() if isinstance(source, torch.Tensor) else np.asarray(source).size) // 3
+    nt = (target.numel() if isinstance(target, torch.Tensor) else np.asarray(target).size) // 3
+    with torch.cuda.device(dev):
+        src = _as_device_f64(source, 3 * ns, dev)
+        trg = _as_device_f64(target, 3 * nt, dev)
+        f = _as_device_f64(force, 3 * ns, dev)
+        rs = _as_device_f64(radius_source, ns, dev)
+        rt = _as_device_f64(radius_target, nt, dev)
+        L = np.zeros(3) if periodic_length is None else np.asarray(
+            periodic_length.cpu() if isinstance(periodic_length, torch.Tensor) else periodic_length, dtype=np.float64)
+        Lc = (ctypes.c_double * 3)(*[float(x) for x in L.reshape(-1)[:3]])
+        if out is None:
+            out = torch.empty(3 * nt, dtype=torch.float64, device=dev)
+        if nt > 0:
+            nbytes = lib.rmb_source_target_workspace_bytes(precision, nt, ns, Lc)
+            ws = _workspace(nbytes, dev)
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            _lib.check(lib.rmb_mobility_source_target(
+                wall, precision, flags | default_flags, nt, ns, trg.data_ptr(), src.data_ptr(), f.data_ptr(),
+                rt.data_ptr(), rs.data_ptr(), float(eta), Lc, out.data_ptr(), ws.data_ptr(), ws.numel(), stream))
+        return out.cpu().numpy() if host_in else out
+
+
+def _make_source_target(wall, precision=FP64, doc=""):
+    def f(source, target, force, radius_source, radius_target, eta, *args, **kwargs):
+        return mobility_source_target(wall, source, target, force, radius_source, radius_target, eta,
+                                      periodic_length=kwargs.get("periodic_length"), precision=precision)
+    f.__doc__ = doc
+    return f
+
+
+def mobility_radii_trans_times_force(r_vectors, force, eta, a, radius_blobs, function, *args, **kwargs):
+    """mobility.py:1369: M f for blobs with different radii; `function` is one of the *_source_target_* products
+    (the argument `a` is ignored, as in the reference)."""
+    return function(r_vectors, r_vectors, force, radius_blobs, radius_blobs, eta, *args, **kwargs)
+
+
 def _make(block, wall, flags=0, precision=FP64, doc=""):
     def f(r_vectors, vec, eta, a, *args, **kwargs):
         return mobility_product(block, wall, r_vectors, vec, eta, a,
@@ -123,7 +167,7 @@ _TABLE = [
     ("free_surface_mobility_trans_times_force", UF, FREE_SURFACE, 0, ":1390; :533"),
 ]
 
-__all__ = ["mobility_product"]
+__all__ = ["mobility_product", "mobility_source_target", "mobility_radii_trans_times_force"]
 for _stem, _b, _w, _fl, _ref in _TABLE:
     for _suffix, _prec in (("_b200", FP64), ("_b200_fp32", FP32)):
         _name = _stem + _suffix
@@ -136,5 +180,14 @@ for _wname, _w, _ref in (("single_wall", SINGLE_WALL, ":384"), ("no_wall", NO_WA
         _name = "%s_mobility_trans_times_force_torque%s" % (_wname, _suffix)
         globals()[_name] = _make_fused(_w, _prec, "B200 drop-in for mobility.%s_mobility_trans_times_force_torque_pycuda "
                                        "(mobility/mobility.py%s): UF f + UT t in one pass." % (_wname, _ref))
+        globals()[_name].__name__ = _name
+        __all__.append(_name)
+for _wname, _w, _ref in (("single_wall", SINGLE_WALL, ":494; :551"), ("no_wall", NO_WALL, ":588"),
+                          ("free_surface", FREE_SURFACE, ":1407")):
+    for _suffix, _prec in (("_b200", FP64), ("_b200_fp32", FP32)):
+        _name = "%s_mobility_trans_times_force_source_target%s" % (_wname, _suffix)
+        globals()[_name] = _make_source_target(
+            _w, _prec, "B200 drop-in for mobility.%s_mobility_trans_times_force_source_target_numba / _pycuda "
+            "(mobility/mobility.py%s): separate source / target sets, per-blob radii." % (_wname, _ref))
         globals()[_name].__name__ = _name
         __all__.append(_name)

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "../rigidmultiblobswall_b200/csrc/mf_core.cuh"
+#include "../rigidmultiblobswall_b200/csrc/st_math.cuh"
 
 using namespace rmb;
 
@@ -88,4 +89,54 @@ extern "C" void host_mf(int block, int wall, int fp32, long n, const double* r, 
   const bool per = L[0] > 0 || L[1] > 0 || L[2] > 0;
   if (fp32) run_b<float>(block, wall, per, n, r, va, vb, eta, a, L, in_plane, out);
   else run_b<double>(block, wall, per, n, r, va, vb, eta, a, L, in_plane, out);
+}
+
+// ---- source-target kernels with per-blob radii (csrc/st_math.cuh) ----
+template <typename T, int WALLMODE>
+static void run_st(long nt, long ns, const double* trg, const double* src, const double* f, const double* rt,
+                   const double* rs, double eta, const double* L, double* out)
+{
+  std::vector<StRec<T>> rec(ns);
+  for (long j = 0; j < ns; j++)
+    st_pack<T>(WALLMODE == ST_WALL, src[3 * j], src[3 * j + 1], src[3 * j + 2], rs[j], f[3 * j], f[3 * j + 1],
+               f[3 * j + 2], rec[j]);
+  Periodic<T> P;
+  P.nbox = 1;
+  for (int d = 0; d < 3; d++) {
+    P.per[d] = L[d] > 0;
+    P.L[d] = T(L[d]); P.invL[d] = P.per[d] ? T(1.0 / L[d]) : T(0);
+    if (P.per[d]) P.nbox *= 3;
+  }
+  const double norm = 1.0 / (8.0 * 3.14159265358979323846 * eta);
+  for (long i = 0; i < nt; i++) {
+    StTarget<T> t;
+    const double B = st_target<T>(WALLMODE == ST_WALL, trg[3 * i], trg[3 * i + 1], trg[3 * i + 2], rt[i], t);
+    T ux = 0, uy = 0, uz = 0;
+    for (int b = 0; b < P.nbox; b++) {
+      T sx, sy, sz; bool central;
+      box_shift(P, b, sx, sy, sz, central);
+      for (long j = 0; j < ns; j++) {
+        T rx = t.x - rec[j].x, ry = t.y - rec[j].y, rz = t.z - rec[j].z;
+        if (P.per[0]) rx = wrap_shift(rx, P.L[0], P.invL[0], sx);
+        if (P.per[1]) ry = wrap_shift(ry, P.L[1], P.invL[1], sy);
+        if (P.per[2]) rz = wrap_shift(rz, P.L[2], P.invL[2], sz);
+        pair_st<T, WALLMODE>(t, rx, ry, rz, t.z + rec[j].z, rec[j].z, rec[j].b, rec[j].ib, rec[j].fx, rec[j].fy,
+                             rec[j].fz, ux, uy, uz);
+      }
+    }
+    out[3 * i] = double(ux) * norm * B; out[3 * i + 1] = double(uy) * norm * B; out[3 * i + 2] = double(uz) * norm * B;
+  }
+}
+
+extern "C" void host_st(int wallmode, int fp32, long nt, long ns, const double* trg, const double* src,
+                        const double* f, const double* rt, const double* rs, double eta, const double* L, double* out)
+{
+#define RMB_ST(T)                                                                        \
+  switch (wallmode) {                                                                    \
+    case ST_NO_WALL: run_st<T, ST_NO_WALL>(nt, ns, trg, src, f, rt, rs, eta, L, out); break; \
+    case ST_WALL: run_st<T, ST_WALL>(nt, ns, trg, src, f, rt, rs, eta, L, out); break;   \
+    default: run_st<T, ST_FREE_SURFACE>(nt, ns, trg, src, f, rt, rs, eta, L, out); break; \
+  }
+  if (fp32) { RMB_ST(float) } else { RMB_ST(double) }
+#undef RMB_ST
 }

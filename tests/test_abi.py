@@ -29,12 +29,16 @@ def test_library_exports_every_declared_symbol():
 def test_version_and_argument_errors_without_gpu():
     from rigidmultiblobswall_b200 import _lib
     lib = _lib.load()
-    assert lib.rmb_version() == 100
+    assert lib.rmb_version() == 101
     # argument validation happens before any CUDA call
     rc = lib.rmb_mobility_product(99, 0, 0, 0, 1, 1, 0, None, None, None, 1.0, 1.0, None, None, None, 0, None)
     assert rc == -1 and b"block" in lib.rmb_last_error()
     rc = lib.rmb_mobility_product(0, 0, 0, 0, 5, 4, 0, None, None, None, 1.0, 1.0, None, None, None, 0, None)
     assert rc == -1 and b"target range" in lib.rmb_last_error()
+    rc = lib.rmb_mobility_source_target(7, 0, 0, 1, 1, None, None, None, None, None, 1.0, None, None, None, 0, None)
+    assert rc == -1 and b"wall" in lib.rmb_last_error()
+    rc = lib.rmb_mobility_source_target(1, 0, 0, 3, 2, None, None, None, None, None, 1.0, None, 8, None, 0, None)
+    assert rc == -1 and b"null" in lib.rmb_last_error()
 
 
 def test_python_api_mirrors_reference_names():
@@ -45,6 +49,9 @@ def test_python_api_mirrors_reference_names():
                  "single_wall_mobility_trans_times_force_torque"):
         assert callable(getattr(mb, stem + "_b200"))
         assert callable(getattr(mb, stem + "_b200_fp32"))
+    for wall in ("single_wall", "no_wall", "free_surface"):
+        assert callable(getattr(mb, wall + "_mobility_trans_times_force_source_target_b200"))
+    assert callable(mb.mobility_radii_trans_times_force)
 
 
 def test_product_path_never_imports_the_oracle():
