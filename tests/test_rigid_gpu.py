@@ -136,3 +136,27 @@ def test_stochastic_preconditioner_and_preconditioned_lanczos(rg, setup):
                                 z=dev(rg["stoch/z"]))
     assert abs(it - int(rg["stoch/iterations"][0])) <= 1
     assert relerr(noise, rg["stoch/noise"]) < 1e-8
+
+
+def test_sharded_rigid_system_single_rank_matches_direct_solve(rg):
+    """parallel.ShardedRigidSystem on one rank == rigid.solve_mobility_problem / the preconditioned Lanczos
+    (the world-2 plumbing is covered on CPU by tests/test_parallel_gloo.py)."""
+    from rigidmultiblobswall_b200 import parallel, rigid
+    a, eta, tol = rg["rigid/a_eta_tol"]
+    system = parallel.ShardedRigidSystem(rg["struct/boomerang_N_15"], rg["rigid/location"], rg["rigid/quaternion"],
+                                         eta, a, group=False)
+    assert system.ranges == [(0, 180)] and (system.b0, system.b1) == (0, 12)
+    U, lam, its, info = system.solve_mobility(system.local_slice(rg["rigid/FT"]), tolerance=tol)
+    bodies = rigid.RigidBodies(rg["struct/boomerang_N_15"], rg["rigid/location"], rg["rigid/quaternion"])
+    U0, lam0, its0, info0 = rigid.solve_mobility_problem(bodies, rg["rigid/FT"], eta, a, tolerance=tol)
+    assert info == 0 and its == its0
+    assert relerr(U, U0.cpu().numpy()) < 1e-12 and relerr(lam, lam0.cpu().numpy()) < 1e-12
+    z = torch.from_numpy(np.random.default_rng(4).standard_normal(540)).cuda()
+    noise, it_l = system.stochastic_noise(z, factor=0.7, tolerance=1e-8)
+    assert noise.shape == (540,) and 1 <= it_l < 40
+    # same numbers as the golden-checked single-process path (rigid.build_block_diagonal_preconditioners_det_stoch)
+    from rigidmultiblobswall_b200 import solvers
+    r = bodies.get_r_vectors()
+    _, mobility_pc, P_inv_mult = rigid.build_block_diagonal_preconditioners_det_stoch(bodies, r, 180, eta, a)
+    ref, it_ref = solvers.lanczos(factor=0.7, tolerance=1e-8, mobility_mult=mobility_pc, L_mult=P_inv_mult, z=z)
+    assert it_l == it_ref and relerr(noise, ref.cpu().numpy()) < 1e-12
