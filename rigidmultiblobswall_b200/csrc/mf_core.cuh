@@ -100,21 +100,23 @@ RMB_HD void pair_geometry(const Target<T>& t, T xj, T yj, T zj, const Periodic<T
 
 // One pair, one block.  v = the record's vectors (already zeroed by the
 // caller for the self pair, whose geometry it also made finite).  g.h is the
-// SOURCE height; ht is the TARGET height, which the transposed wall term of
+// SOURCE height; C.ht is the TARGET height, which the transposed wall term of
 // UT uses instead (mobility_numba.py:651).
-template <typename T, int BLOCK, bool WALL>
-RMB_HD void pair_apply(const PairGeom<T>& g, T ht, const T* v, bool any_near, T r2, T rxy2, T& ux, T& uy, T& uz)
+template <typename T, int BLOCK, bool WALL, bool ZOPEN = false>
+RMB_HD void pair_apply(const PairGeom<T>& g, const UfCtx<T>& C, const T* v, bool any_near, T r2, T rxy2, T& ux, T& uy,
+                       T& uz)
 {
-  if (BLOCK == UF || BLOCK == UF_UT) pair_uf<T, WALL>(g, ht, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
+  const T ht = C.ht;
+  if (BLOCK == UF || BLOCK == UF_UT) pair_uf<T, WALL, ZOPEN>(g, C, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
   if (BLOCK == WF) pair_wf<T, WALL>(g, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
   if (BLOCK == WT) pair_wt<T, WALL>(g, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
   if (BLOCK == UF_FS) {
     // free surface (mobility_numba.py:1770-1937): RPY(r) f + RPY(R) f', R = (rx, ry, z_i+z_j), f' = (fx, fy, -fz)
     // (the image block enters with the sign pattern [+ + -; + + -; + + -] on its columns, :1918-1926)
-    pair_uf<T, false>(g, ht, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
+    pair_uf<T, false>(g, C, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
     PairGeom<T> gi = g;
     gi.rz = g.Rz;
-    pair_uf<T, false>(gi, ht, v[0], v[1], -v[2], true, RMB_FMA(g.Rz, g.Rz, rxy2), rxy2, ux, uy, uz);
+    pair_uf<T, false>(gi, C, v[0], v[1], -v[2], true, RMB_FMA(g.Rz, g.Rz, rxy2), rxy2, ux, uy, uz);
   }
   if (BLOCK == UT || BLOCK == UF_UT) {
     PairGeom<T> gt = g;
@@ -138,7 +140,7 @@ RMB_HD void self_apply(T h, const T* v, T& ux, T& uy, T& uz)
     self_uf<T, false>(h, v[0], v[1], v[2], ux, uy, uz);
     PairGeom<T> gi;
     gi.rx = T(0); gi.ry = T(0); gi.rz = h + h; gi.Rz = gi.rz; gi.h = h;
-    pair_uf<T, false>(gi, h, v[0], v[1], -v[2], true, gi.rz * gi.rz, T(0), ux, uy, uz);
+    pair_uf<T, false>(gi, make_uf_ctx<T>(h), v[0], v[1], -v[2], true, gi.rz * gi.rz, T(0), ux, uy, uz);
   }
 }
 

@@ -20,9 +20,11 @@
 #if defined(RMB_HOST_ONLY)
 #include <cmath>
 #define RMB_HD inline
+#define RMB_HOST_DEVICE inline
 #define RMB_FMA(a, b, c) std::fma((a), (b), (c))
 #else
 #define RMB_HD __device__ __forceinline__
+#define RMB_HOST_DEVICE __host__ __device__ __forceinline__
 #define RMB_FMA(a, b, c) fma((a), (b), (c))
 #endif
 
@@ -89,23 +91,54 @@ struct PairGeom {
 //   p4 = 2H - (20/3) Rz t^2
 //   p5 = -4H^2 - (4 alpha + 8/3) t + 20 k t
 //   u += q p1 f + q^3 [ (p2 (R.f) + p3 f_z) R + z^ (p4 (R.f) + p5 f_z) ]
-// 71 FP64 instructions per far pair in total (was 203 flop as the reference
-// writes it).  any_near: warp-uniform flag "some lane has r2 < 4" -- the near
+// Evaluation order (every FMA has at most ONE literal operand, and the
+// literals with a non-zero low word come from UfCtx, i.e. from the kernel's
+// constant bank, so the loop holds no constant-materialising moves):
+//   Aq = alpha + 1/3, X = Aq - (5/3) k, Y = Aq - (7/3) k, Wv = Aq + 1/3 - 5k
+//   b2 = (2 h_i) H + 2/3                                  (2 h_i per target; 6 beta + 2 = 3 b2)
+//   p1 = -1 + t (2t X - b2)          v = 3 b2 - 10 t Y = 3 v3,   p2 = -1 + t v
+//   p3 = 2 [H - Rz t (v - (10/3) t)]                     p4 = 2 [H - Rz t (10/3) t]
+//   p5 = -4 [H^2 + t Wv]
+// and the factors 2 and 4 ride on 2 f_z: 45 FP64 instructions for the wall part.
+// ZOPEN (no wrap in z, i.e. rz = z_i - z_j): |R|^2 = r^2 + 4 h_i h_j instead of rx^2 + ry^2 + Rz^2.
+// any_near: warp-uniform flag "some lane has r2 < 4" -- the near
 // coefficients are only evaluated when it is set.
-template <typename T, bool WALL>
-RMB_HD void pair_uf(const PairGeom<T>& p, T ht, T fx, T fy, T fz, bool any_near, T r2, T rxy2, T& ux, T& uy, T& uz)
+template <typename T>
+struct UfCtx {
+  T c13, c23, cm53, cm73, c103, c43;   // 1/3, 2/3, -5/3, -7/3, 10/3, 4/3
+  T ht, ht2, ht4;                      // target height h_i and its multiples (wall form)
+};
+
+template <typename T>
+RMB_HOST_DEVICE UfCtx<T> make_uf_ctx(T ht)
+{
+  UfCtx<T> C;
+  C.c13 = T(1.0 / 3.0); C.c23 = T(2.0 / 3.0); C.cm53 = T(-5.0 / 3.0); C.cm73 = T(-7.0 / 3.0);
+  C.c103 = T(10.0 / 3.0); C.c43 = T(4.0 / 3.0);
+  C.ht = ht; C.ht2 = T(2.0) * ht; C.ht4 = T(4.0) * ht;
+  return C;
+}
+template <typename T>
+RMB_HD void set_target_height(UfCtx<T>& C, T ht)
+{
+  C.ht = ht; C.ht2 = T(2.0) * ht; C.ht4 = T(4.0) * ht;
+}
+
+template <typename T, bool WALL, bool ZOPEN = false>
+RMB_HD void pair_uf(const PairGeom<T>& p, const UfCtx<T>& C, T fx, T fy, T fz, bool any_near, T r2, T rxy2, T& ux,
+                    T& uy, T& uz)
 {
   const T s = RMB_FMA(p.ry, fy, p.rx * fx);
   const T invr = rsqrt_full(r2);
   const T invr2 = invr * invr;
   const T rf = RMB_FMA(p.rz, fz, s);
   const T invr3 = invr2 * invr;
-  T A = RMB_FMA(T(2.0 / 3.0), invr3, invr);          // (1 + 2/(3 r^2)) / r
+  T A = RMB_FMA(C.c23, invr3, invr);                 // (1 + 2/(3 r^2)) / r
   const T rfi = rf * invr3;
   T B = RMB_FMA(T(-2.0), invr2 * rfi, rfi);          // (1 - 2/r^2) (r.f) / r^3
   if (any_near) {
     const T r = r2 * invr;
-    const T An = RMB_FMA(T(-0.375), r, T(4.0 / 3.0));
+    const T An = RMB_FMA(T(-0.375), r, C.c43);
     const T Bn = (T(0.125) * invr) * rf;
     const bool near = lt4(r2);
     A = near ? An : A;
@@ -115,34 +148,34 @@ RMB_HD void pair_uf(const PairGeom<T>& p, T ht, T fx, T fy, T fz, bool any_near,
     ux = RMB_FMA(A, fx, ux); uy = RMB_FMA(A, fy, uy); uz = RMB_FMA(A, fz, uz);
     ux = RMB_FMA(B, p.rx, ux); uy = RMB_FMA(B, p.ry, uy); uz = RMB_FMA(B, p.rz, uz);
   } else {
-    const T al = p.Rz * p.Rz;
-    const T q = rsqrt_full(rxy2 + al);
+    // |R|^2 = rx^2 + ry^2 + Rz^2.  Without a z wrap rz = z_i - z_j, so |R|^2 = r^2 + 4 h_i h_j (one FMA, no Rz^2).
+    const T q = rsqrt_full(ZOPEN ? RMB_FMA(C.ht4, p.h, r2) : RMB_FMA(p.Rz, p.Rz, rxy2));
     const T t = q * q;
-    const T q3 = q * t;
-    const T be = ht * p.h;
-    const T k = al * t;
-    T p1 = RMB_FMA(T(-10.0 / 3.0), k, RMB_FMA(T(2.0), al, T(2.0 / 3.0)));
-    p1 = RMB_FMA(p1, t, -RMB_FMA(T(2.0), be, T(2.0 / 3.0)));
-    p1 = RMB_FMA(p1, t, T(-1.0));
-    T p2 = RMB_FMA(T(70.0 / 3.0), k, -RMB_FMA(T(10.0), al, T(10.0 / 3.0)));
-    p2 = RMB_FMA(p2, t, RMB_FMA(T(6.0), be, T(2.0)));
-    p2 = RMB_FMA(p2, t, T(-1.0));
-    T i3 = RMB_FMA(T(-140.0 / 3.0), k, RMB_FMA(T(20.0), al, T(40.0 / 3.0)));
-    i3 = RMB_FMA(i3, t, -RMB_FMA(T(12.0), be, T(4.0)));
+    const T Aq = RMB_FMA(p.Rz, p.Rz, C.c13);             // alpha + 1/3
     const T Zt = p.Rz * t;
-    const T H2 = p.h + p.h;
-    const T p3 = RMB_FMA(i3, Zt, H2);
-    const T p4 = RMB_FMA(T(-20.0 / 3.0) * Zt, t, H2);
-    T p5 = RMB_FMA(T(20.0), k, -RMB_FMA(T(4.0), al, T(8.0 / 3.0)));
-    p5 = RMB_FMA(p5, t, -(H2 * H2));
+    const T t2 = t + t;
+    const T k = p.Rz * Zt;                               // alpha t
+    const T q3 = q * t;
+    const T b2 = RMB_FMA(C.ht2, p.h, C.c23);             // 2 beta + 2/3
+    const T X = RMB_FMA(C.cm53, k, Aq);
+    const T Y = RMB_FMA(C.cm73, k, Aq);
+    const T p1 = RMB_FMA(RMB_FMA(t2, X, -b2), t, T(-1.0));
+    const T t103 = C.c103 * t;
+    const T v3 = RMB_FMA(-t103, Y, b2);                  // v / 3, v = (6 beta + 2) - 10 t Y;  p2 = -1 + t v
+    const T p2 = RMB_FMA(v3, T(3.0) * t, T(-1.0));
+    const T p3h = RMB_FMA(-Zt, RMB_FMA(T(3.0), v3, -t103), p.h);   // p3 / 2 = H - Rz t (v - (10/3) t)
+    const T p4h = RMB_FMA(-Zt, t103, p.h);               // p4 / 2
+    const T Wv = RMB_FMA(T(-5.0), k, Aq + C.c13);
+    const T p5q = RMB_FMA(t, Wv, p.h * p.h);             // -p5 / 4
+    const T fz2 = fz + fz;
     const T Rf = RMB_FMA(p.Rz, fz, s);
-    const T SR = RMB_FMA(p2, Rf, p3 * fz) * q3;
-    const T SZ = RMB_FMA(p4, Rf, p5 * fz);
+    const T G = RMB_FMA(p2, Rf, p3h * fz2);              // p2 (R.f) + p3 f_z
+    const T SZh = RMB_FMA(p4h, Rf, -(p5q * fz2));        // (p4 (R.f) + p5 f_z) / 2
     const T Af = RMB_FMA(q, p1, A);
-    const T Bx = B + SR;
+    const T Bx = RMB_FMA(q3, G, B);
     ux = RMB_FMA(Af, fx, ux); uy = RMB_FMA(Af, fy, uy); uz = RMB_FMA(Af, fz, uz);
     ux = RMB_FMA(Bx, p.rx, ux); uy = RMB_FMA(Bx, p.ry, uy);
-    uz = RMB_FMA(B, p.rz, uz); uz = RMB_FMA(SR, p.Rz, uz); uz = RMB_FMA(q3, SZ, uz);
+    uz = RMB_FMA(B, p.rz, uz); uz = RMB_FMA(q3, RMB_FMA(G, p.Rz, SZh + SZh), uz);
   }
 }
 

@@ -32,7 +32,10 @@ namespace {
 #define RMB_TILE 256
 #endif
 #ifndef RMB_UNROLL
-#define RMB_UNROLL 2
+#define RMB_UNROLL 4      // source-loop unroll of the open-boundary kernels
+#endif
+#ifndef RMB_UNROLL_PER
+#define RMB_UNROLL_PER 2  // same for the pseudo-periodic kernels (more live registers per pair)
 #endif
 #ifndef RMB_MINB
 #define RMB_MINB 1
@@ -116,6 +119,7 @@ struct MfArgs {
   const double* damp;
   double norm;
   int in_plane;
+  UfCtx<T> K;        // literal constants of pair_uf (host-filled: read from the constant bank, never materialised)
 };
 
 // Pairs of one target with the `cnt` sources of one shared-memory tile.
@@ -124,11 +128,13 @@ struct MfArgs {
 // is added once per target in the epilogue.
 template <typename T, int BLOCK, bool WALL, bool PERIODIC, bool DIAG>
 __device__ __forceinline__ void tile_pairs(const T* __restrict__ tile, int cnt, long j0, long gi, const Target<T>& t,
+                                           const UfCtx<T>& C,
                                            const Periodic<T>& P, T sx, T sy, T sz, T inva, T& ux, T& uy, T& uz)
 {
   constexpr int NV = (BLOCK == UF_UT) ? 2 : 1;
   constexpr int W = RecWords<T, NV>::value;
-RMB_UNROLL_N(RMB_UNROLL)
+  constexpr int UNROLL = PERIODIC ? RMB_UNROLL_PER : RMB_UNROLL;
+#pragma unroll UNROLL
   for (int j = 0; j < cnt; j++) {
     T w[W];
     load_rec<W>(tile + j * W, w);
@@ -142,7 +148,7 @@ RMB_UNROLL_N(RMB_UNROLL)
       for (int c = 3; c < 3 + 3 * NV; c++) w[c] = self ? T(0) : w[c];
     }
     const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-    pair_apply<T, BLOCK, WALL>(g, t.h, w + 3, any_near, r2, rxy2, ux, uy, uz);
+    pair_apply<T, BLOCK, WALL, !PERIODIC>(g, C, w + 3, any_near, r2, rxy2, ux, uy, uz);
   }
 }
 
@@ -167,6 +173,8 @@ __global__ void __launch_bounds__(TPB, RMB_MINB) mf_kernel(const __grid_constant
     t.x = me.x; t.y = me.y; t.z = me.z;
     t.h = PERIODIC ? me.z * A.inva : me.z;
   }
+  UfCtx<T> C = A.K;
+  set_target_height(C, t.h);
   const int v0 = blockIdx.y * A.vt_per_split;
   const int v1 = min(v0 + A.vt_per_split, A.n_vt);
   const T* srcw = reinterpret_cast<const T*>(A.src);
@@ -210,8 +218,8 @@ __global__ void __launch_bounds__(TPB, RMB_MINB) mf_kernel(const __grid_constant
     const int cnt = (int)min((long)TILE, A.n_src - j0);
     const bool diag = central && (j0 < blk_g1) && (j0 + cnt > blk_g0);
     const T* tp = tile[TMA ? stage : 0];
-    if (diag) tile_pairs<T, BLOCK, WALL, PERIODIC, true>(tp, cnt, j0, gi, t, A.P, sx, sy, sz, A.inva, ux, uy, uz);
-    else tile_pairs<T, BLOCK, WALL, PERIODIC, false>(tp, cnt, j0, gi, t, A.P, sx, sy, sz, A.inva, ux, uy, uz);
+    if (diag) tile_pairs<T, BLOCK, WALL, PERIODIC, true>(tp, cnt, j0, gi, t, C, A.P, sx, sy, sz, A.inva, ux, uy, uz);
+    else tile_pairs<T, BLOCK, WALL, PERIODIC, false>(tp, cnt, j0, gi, t, C, A.P, sx, sy, sz, A.inva, ux, uy, uz);
     __syncthreads();
     if (TMA) stage ^= 1;
   }
@@ -353,6 +361,7 @@ int launch(const Call& c)
   A.damp = damp;
   A.norm = block_norm(BLOCK, c.eta, c.a);
   A.in_plane = in_plane;
+  A.K = make_uf_ctx<T>(T(0));
 
   const dim3 grid((unsigned)p.tgt_blocks, (unsigned)p.n_split);
   if (c.flags & RMB_NO_TMA) mf_kernel<T, BLOCK, WALL, PERIODIC, false><<<grid, TPB, 0, c.stream>>>(A);

@@ -156,7 +156,7 @@ __global__ void body_blocks_kernel(long n_bodies, const long* __restrict__ body_
           double r2, rxy2;
           pair_geometry<double, WALL, false>(t, r[3 * (i0 + j)] * inva, r[3 * (i0 + j) + 1] * inva, zj * inva, P, 0.0,
                                              0.0, 0.0, inva, g, r2, rxy2);
-          pair_apply<double, UF, WALL>(g, t.h, e, true, r2, rxy2, ux, uy, uz);
+          pair_apply<double, UF, WALL>(g, make_uf_ctx<double>(t.h), e, true, r2, rxy2, ux, uy, uz);
         }
         const double sc = norm * Bi * Bj;
         blk[c] = ux * sc; blk[3 + c] = uy * sc; blk[6 + c] = uz * sc;

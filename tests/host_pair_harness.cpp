@@ -49,7 +49,7 @@ static void run(long n, const double* r, const double* va, const double* vb, dou
         if (central && j == i) continue;
         PairGeom<T> g; T r2, rxy2;
         pair_geometry<T, WALL, PERIODIC>(t, rec[j].x, rec[j].y, rec[j].z, P, sx, sy, sz, T(inva), g, r2, rxy2);
-        pair_apply<T, BLOCK, WALL>(g, t.h, rec[j].v, lt4(r2), r2, rxy2, ux, uy, uz);
+        pair_apply<T, BLOCK, WALL, !PERIODIC>(g, make_uf_ctx<T>(t.h), rec[j].v, lt4(r2), r2, rxy2, ux, uy, uz);
       }
     }
     self_apply<T, BLOCK, WALL>(t.h, rec[i].v, ux, uy, uz);
