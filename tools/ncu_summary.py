@@ -1,0 +1,40 @@
+"""Dev tool: text summaries of the ncu artefacts gpurun brought back.
+  python tools/ncu_summary.py full  gpurun_out/<tag>_mf_full.ncu-rep   > profiles/<tag>_mf_kernel_ncu_summary.txt
+  python tools/ncu_summary.py list  gpurun_out/<tag>_launches.csv      > profiles/<tag>_launch_shares.txt"""
+import collections, csv, io, re, subprocess, sys
+
+KEEP = re.compile(r"^(dram__bytes_(read|write)\.sum$|gpu__time_duration\.sum|launch__(block_size|grid_size|registers_per_thread|"
+                  r"waves_per_multiprocessor|occupancy_limit_(registers|shared_mem))|sm__inst_executed_pipe_(alu|fma|fp64|lsu|xu|uniform)"
+                  r"\.avg\.pct_of_peak_sustained_active|sm__pipe_fp64_cycles_active\.avg\.pct|sm__throughput\.avg\.pct|"
+                  r"sm__warps_active\.avg\.pct_of_peak_sustained_active|smsp__average_warps_issue_stalled_.*_per_issue_active|"
+                  r"smsp__inst_executed\.sum$|smsp__inst_executed_pipe_fp64\.sum$|sm__inst_executed_pipe_fp64\.sum$|smsp__issue_active\.avg\.pct|"
+                  r"l1tex__data_pipe_lsu_wavefronts_mem_shared\.sum$|sm__cycles_elapsed\.max|lts__t_sector_hit_rate\.pct|smsp__cycles_active\.avg$|sm__inst_executed\.sum$)")
+
+def full(path):
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    names, units, vals = rows[0], rows[1], rows[2]
+    for n, u, v in zip(names, units, vals):
+        if n == "Kernel Name":
+            print("# kernel:", v)
+        if KEEP.search(n):
+            print("%-90s %-16s %s" % (n, u, v))
+
+def launches(path):
+    txt = open(path).read()
+    txt = txt[txt.index('"ID"'):]
+    agg = collections.defaultdict(lambda: [0, 0.0])
+    for row in csv.DictReader(io.StringIO(txt)):
+        if row.get("Metric Name") != "gpu__time_duration.sum":
+            continue
+        v = float(row["Metric Value"].replace(",", ""))
+        if row["Metric Unit"] in ("us", "usecond"): v *= 1e3
+        if row["Metric Unit"] in ("ms", "msecond"): v *= 1e6
+        k = re.sub(r"\(.*", "", row["Kernel Name"])[:70]
+        agg[k][0] += 1; agg[k][1] += v
+    tot = sum(v[1] for v in agg.values())
+    print("# kernel, launches, total ns, share")
+    for k, (n, t) in sorted(agg.items(), key=lambda x: -x[1][1])[:25]:
+        print("%-72s %6d %14.0f %6.2f%%" % (k, n, t, 100 * t / tot))
+
+{"full": full, "list": launches}[sys.argv[1]](sys.argv[2])
