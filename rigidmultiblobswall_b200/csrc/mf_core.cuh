@@ -98,6 +98,63 @@ RMB_HD void pair_geometry(const Target<T>& t, T xj, T yj, T zj, const Periodic<T
   r2 = RMB_FMA(g.rz, g.rz, rxy2);
 }
 
+// Pseudo-periodic pair in two parts, so that the wrap, the 1/a scaling and the
+// record load are paid once per (target, source) and not once per image box.
+// Part 1, per source: minimum-image wrap in the caller's length unit (where the
+// reference does it, mobility_numba.py:184-192), then 1/a.  The wall term uses
+// the unwrapped z_i + z_j (:242).
+template <typename T, bool WALL>
+RMB_HD void periodic_base(const Target<T>& t, T xj, T yj, T zj, const Periodic<T>& P, T inva, PairGeom<T>& g0)
+{
+  g0.rx = t.x - xj; g0.ry = t.y - yj; g0.rz = t.z - zj;
+  if (P.per[0]) g0.rx = wrap_shift(g0.rx, P.L[0], P.invL[0], T(0));
+  if (P.per[1]) g0.ry = wrap_shift(g0.ry, P.L[1], P.invL[1], T(0));
+  if (P.per[2]) g0.rz = wrap_shift(g0.rz, P.L[2], P.invL[2], T(0));
+  g0.rx *= inva; g0.ry *= inva; g0.rz *= inva;
+  g0.Rz = T(0); g0.h = T(0);
+  if (WALL) {
+    g0.Rz = (t.z + zj) * inva;
+    g0.h = zj * inva;
+  }
+}
+
+// All image boxes of the periodic directions: shift vectors box * L / a in the
+// nesting order of the reference loops (x slowest, z fastest, -1, 0, +1 each).
+template <typename T>
+struct BoxTable {
+  T s[27][3];
+  int n, central;
+};
+
+template <typename T>
+inline BoxTable<T> make_box_table(const Periodic<T>& P, double inva)
+{
+  BoxTable<T> B;
+  B.n = P.nbox; B.central = 0;
+  for (int b = 0; b < 27; b++) {
+    int k[3] = {0, 0, 0}, c = b;
+    if (b < P.nbox)
+      for (int d = 2; d >= 0; --d)
+        if (P.per[d]) { k[d] = (c % 3) - 1; c /= 3; }
+    for (int d = 0; d < 3; d++) B.s[b][d] = T(k[d] * (double)P.L[d] * inva);
+    if (b < P.nbox && k[0] == 0 && k[1] == 0 && k[2] == 0) B.central = b;
+  }
+  return B;
+}
+
+// Part 2, per image box: add the shift (already in units of a).
+template <typename T>
+RMB_HD void periodic_box(const PairGeom<T>& g0, const Periodic<T>& P, const T* shift, PairGeom<T>& g, T& r2, T& rxy2)
+{
+  (void)P;   // the shift of a non-periodic direction is 0: branch-free
+  g.Rz = g0.Rz; g.h = g0.h;
+  g.rx = g0.rx + shift[0];
+  g.ry = g0.ry + shift[1];
+  g.rz = g0.rz + shift[2];
+  rxy2 = RMB_FMA(g.ry, g.ry, g.rx * g.rx);
+  r2 = RMB_FMA(g.rz, g.rz, rxy2);
+}
+
 // One pair, one block.  v = the record's vectors (already zeroed by the
 // caller for the self pair, whose geometry it also made finite).  g.h is the
 // SOURCE height; C.ht is the TARGET height, which the transposed wall term of

@@ -111,7 +111,7 @@ struct MfArgs {
   Periodic<T> P;
   T inva;
   int n_tiles;       // ceil(n_src / TILE)
-  int n_vt;          // virtual tiles = n_boxes * n_tiles
+  int n_vt;          // = n_tiles (image boxes are looped inside the pair loop)
   int vt_per_split;  // virtual tiles handled by one blockIdx.y
   int n_split;
   T* partial;        // [n_split][n_tgt][3] when n_split > 1
@@ -119,6 +119,7 @@ struct MfArgs {
   const double* damp;
   double norm;
   int in_plane;
+  BoxTable<T> box;   // image-box shifts / a (pseudo-periodic kernels)
   UfCtx<T> K;        // literal constants of pair_uf (host-filled: read from the constant bank, never materialised)
 };
 
@@ -128,27 +129,56 @@ struct MfArgs {
 // is added once per target in the epilogue.
 template <typename T, int BLOCK, bool WALL, bool PERIODIC, bool DIAG>
 __device__ __forceinline__ void tile_pairs(const T* __restrict__ tile, int cnt, long j0, long gi, const Target<T>& t,
-                                           const UfCtx<T>& C,
-                                           const Periodic<T>& P, T sx, T sy, T sz, T inva, T& ux, T& uy, T& uz)
+                                           const UfCtx<T>& C, const Periodic<T>& P, const BoxTable<T>& box, T inva,
+                                           T& ux, T& uy, T& uz)
 {
   constexpr int NV = (BLOCK == UF_UT) ? 2 : 1;
   constexpr int W = RecWords<T, NV>::value;
-  constexpr int UNROLL = PERIODIC ? RMB_UNROLL_PER : RMB_UNROLL;
-#pragma unroll UNROLL
-  for (int j = 0; j < cnt; j++) {
-    T w[W];
-    load_rec<W>(tile + j * W, w);
-    PairGeom<T> g;
-    T r2, rxy2;
-    pair_geometry<T, WALL, PERIODIC>(t, w[0], w[1], w[2], P, sx, sy, sz, inva, g, r2, rxy2);
-    if (DIAG) {
-      const bool self = (j0 + j == gi);
-      if (self) { r2 = T(1); rxy2 = T(1); }
+  constexpr int U_OPEN = RMB_UNROLL, U_PER = RMB_UNROLL_PER;
+  if constexpr (!PERIODIC) {
+#pragma unroll U_OPEN
+    for (int j = 0; j < cnt; j++) {
+      T w[W];
+      load_rec<W>(tile + j * W, w);
+      PairGeom<T> g;
+      T r2, rxy2;
+      pair_geometry<T, WALL, false>(t, w[0], w[1], w[2], P, T(0), T(0), T(0), inva, g, r2, rxy2);
+      if (DIAG) {
+        const bool self = (j0 + j == gi);
+        if (self) { r2 = T(1); rxy2 = T(1); }
 #pragma unroll
-      for (int c = 3; c < 3 + 3 * NV; c++) w[c] = self ? T(0) : w[c];
+        for (int c = 3; c < 3 + 3 * NV; c++) w[c] = self ? T(0) : w[c];
+      }
+      const bool any_near = __any_sync(0xffffffffu, lt4(r2));
+      pair_apply<T, BLOCK, WALL, true>(g, C, w + 3, any_near, r2, rxy2, ux, uy, uz);
     }
-    const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-    pair_apply<T, BLOCK, WALL, !PERIODIC>(g, C, w + 3, any_near, r2, rxy2, ux, uy, uz);
+  } else {
+    // image boxes innermost: record load, wrap and 1/a once per source, one shift add per box
+#pragma unroll 1
+    for (int j = 0; j < cnt; j++) {
+      T w[W];
+      load_rec<W>(tile + j * W, w);
+      PairGeom<T> g0;
+      periodic_base<T, WALL>(t, w[0], w[1], w[2], P, inva, g0);
+      const bool self_j = DIAG && (j0 + j == gi);
+#pragma unroll U_PER
+      for (int b = 0; b < box.n; b++) {
+        PairGeom<T> g;
+        T r2, rxy2;
+        periodic_box<T>(g0, P, box.s[b], g, r2, rxy2);
+        T v[3 * NV];
+#pragma unroll
+        for (int c = 0; c < 3 * NV; c++) v[c] = w[3 + c];
+        if (DIAG) {
+          const bool self = self_j && (b == box.central);
+          if (self) { r2 = T(1); rxy2 = T(1); }
+#pragma unroll
+          for (int c = 0; c < 3 * NV; c++) v[c] = self ? T(0) : v[c];
+        }
+        const bool any_near = __any_sync(0xffffffffu, lt4(r2));
+        pair_apply<T, BLOCK, WALL, false>(g, C, v, any_near, r2, rxy2, ux, uy, uz);
+      }
+    }
   }
 }
 
@@ -188,7 +218,7 @@ __global__ void __launch_bounds__(TPB, RMB_MINB) mf_kernel(const __grid_constant
     __syncthreads();
     if (tid == 0 && v0 < v1) {
       mbar_expect_tx(&full[0], TILE_BYTES);
-      bulk_g2s(tile[0], srcw + (size_t)(v0 % A.n_tiles) * TILE * W, TILE_BYTES, &full[0]);
+      bulk_g2s(tile[0], srcw + (size_t)v0 * TILE * W, TILE_BYTES, &full[0]);
     }
   }
 
@@ -196,13 +226,12 @@ __global__ void __launch_bounds__(TPB, RMB_MINB) mf_kernel(const __grid_constant
   int stage = 0;
   uint32_t phases = 0;
   for (int v = v0; v < v1; v++) {
-    const int box = v / A.n_tiles;
-    const int tl = v - box * A.n_tiles;
+    const int tl = v;
     if (TMA) {
       // stage^1 was last read in iteration v-1, which ended with __syncthreads
       if (tid == 0 && v + 1 < v1) {
         mbar_expect_tx(&full[stage ^ 1], TILE_BYTES);
-        bulk_g2s(tile[stage ^ 1], srcw + (size_t)((v + 1) % A.n_tiles) * TILE * W, TILE_BYTES, &full[stage ^ 1]);
+        bulk_g2s(tile[stage ^ 1], srcw + (size_t)(v + 1) * TILE * W, TILE_BYTES, &full[stage ^ 1]);
       }
       mbar_wait(&full[stage], (phases >> stage) & 1u);
       phases ^= (1u << stage);
@@ -211,15 +240,12 @@ __global__ void __launch_bounds__(TPB, RMB_MINB) mf_kernel(const __grid_constant
       for (int k = tid; k < TILE * W; k += TPB) tile[0][k] = gsrc[k];
       __syncthreads();
     }
-    T sx = 0, sy = 0, sz = 0;
-    bool central = true;
-    if (PERIODIC) box_shift(A.P, box, sx, sy, sz, central);
     const long j0 = (long)tl * TILE;
     const int cnt = (int)min((long)TILE, A.n_src - j0);
-    const bool diag = central && (j0 < blk_g1) && (j0 + cnt > blk_g0);
+    const bool diag = (j0 < blk_g1) && (j0 + cnt > blk_g0);
     const T* tp = tile[TMA ? stage : 0];
-    if (diag) tile_pairs<T, BLOCK, WALL, PERIODIC, true>(tp, cnt, j0, gi, t, C, A.P, sx, sy, sz, A.inva, ux, uy, uz);
-    else tile_pairs<T, BLOCK, WALL, PERIODIC, false>(tp, cnt, j0, gi, t, C, A.P, sx, sy, sz, A.inva, ux, uy, uz);
+    if (diag) tile_pairs<T, BLOCK, WALL, PERIODIC, true>(tp, cnt, j0, gi, t, C, A.P, A.box, A.inva, ux, uy, uz);
+    else tile_pairs<T, BLOCK, WALL, PERIODIC, false>(tp, cnt, j0, gi, t, C, A.P, A.box, A.inva, ux, uy, uz);
     __syncthreads();
     if (TMA) stage ^= 1;
   }
@@ -302,7 +328,7 @@ int make_plan(int block, int precision, long n_tgt, long n_src, const double* L,
   p.n_tiles = (int)((n_src + TILE - 1) / TILE);
   p.n_boxes = 1;
   if (L) for (int d = 0; d < 3; d++) if (L[d] > 0) p.n_boxes *= 3;
-  p.n_vt = p.n_tiles * p.n_boxes;
+  p.n_vt = p.n_tiles;   // image boxes are looped inside the pair loop, not as extra tiles
   p.tgt_blocks = (int)((n_tgt + TPB - 1) / TPB);
   // Source splitting (blockIdx.y): used when the target CTAs alone would give
   // fewer than RMB_WAVES waves of resident CTAs (tail effect / idle SMs).  A
@@ -355,6 +381,7 @@ int launch(const Call& c)
     A.P.invL[d] = A.P.per[d] ? T(1.0 / c.L[d]) : T(0);
   }
   A.inva = T(1.0 / c.a);
+  A.box = make_box_table<T>(A.P, 1.0 / c.a);
   A.n_tiles = p.n_tiles; A.n_vt = p.n_vt; A.vt_per_split = p.vt_per_split; A.n_split = p.n_split;
   A.partial = reinterpret_cast<T*>(c.ws + p.off_partial);
   A.out = c.out;

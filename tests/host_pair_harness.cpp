@@ -42,14 +42,26 @@ static void run(long n, const double* r, const double* va, const double* vb, dou
     t.x = rec[i].x; t.y = rec[i].y; t.z = rec[i].z;
     t.h = PERIODIC ? T(rec[i].z * T(inva)) : rec[i].z;
     T ux = 0, uy = 0, uz = 0;
-    for (int b = 0; b < P.nbox; b++) {
-      T sx, sy, sz; bool central;
-      box_shift(P, b, sx, sy, sz, central);
+    const UfCtx<T> C = make_uf_ctx<T>(t.h);
+    if (!PERIODIC) {
       for (long j = 0; j < n; j++) {
-        if (central && j == i) continue;
+        if (j == i) continue;
         PairGeom<T> g; T r2, rxy2;
-        pair_geometry<T, WALL, PERIODIC>(t, rec[j].x, rec[j].y, rec[j].z, P, sx, sy, sz, T(inva), g, r2, rxy2);
-        pair_apply<T, BLOCK, WALL, !PERIODIC>(g, make_uf_ctx<T>(t.h), rec[j].v, lt4(r2), r2, rxy2, ux, uy, uz);
+        pair_geometry<T, WALL, false>(t, rec[j].x, rec[j].y, rec[j].z, P, T(0), T(0), T(0), T(inva), g, r2, rxy2);
+        pair_apply<T, BLOCK, WALL, true>(g, C, rec[j].v, lt4(r2), r2, rxy2, ux, uy, uz);
+      }
+    } else {
+      // same two-part geometry as the kernel: wrap + 1/a per source, shift per image box
+      const BoxTable<T> box = make_box_table<T>(P, inva);
+      for (long j = 0; j < n; j++) {
+        PairGeom<T> g0;
+        periodic_base<T, WALL>(t, rec[j].x, rec[j].y, rec[j].z, P, T(inva), g0);
+        for (int b = 0; b < box.n; b++) {
+          if (b == box.central && j == i) continue;
+          PairGeom<T> g; T r2, rxy2;
+          periodic_box<T>(g0, P, box.s[b], g, r2, rxy2);
+          pair_apply<T, BLOCK, WALL, false>(g, C, rec[j].v, lt4(r2), r2, rxy2, ux, uy, uz);
+        }
       }
     }
     self_apply<T, BLOCK, WALL>(t.h, rec[i].v, ux, uy, uz);
