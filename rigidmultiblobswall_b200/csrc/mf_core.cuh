@@ -163,10 +163,9 @@ template <typename T, int BLOCK, bool WALL, bool ZOPEN = false>
 RMB_HD void pair_apply(const PairGeom<T>& g, const UfCtx<T>& C, const T* v, bool any_near, T r2, T rxy2, T& ux, T& uy,
                        T& uz)
 {
-  const T ht = C.ht;
   if (BLOCK == UF || BLOCK == UF_UT) pair_uf<T, WALL, ZOPEN>(g, C, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
-  if (BLOCK == WF) pair_wf<T, WALL>(g, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
-  if (BLOCK == WT) pair_wt<T, WALL>(g, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
+  if (BLOCK == WF) pair_wf<T, WALL, ZOPEN>(g, C, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
+  if (BLOCK == WT) pair_wt<T, WALL, ZOPEN>(g, C, v[0], v[1], v[2], any_near, r2, rxy2, ux, uy, uz);
   if (BLOCK == UF_FS) {
     // free surface (mobility_numba.py:1770-1937): RPY(r) f + RPY(R) f', R = (rx, ry, z_i+z_j), f' = (fx, fy, -fz)
     // (the image block enters with the sign pattern [+ + -; + + -; + + -] on its columns, :1918-1926)
@@ -176,10 +175,8 @@ RMB_HD void pair_apply(const PairGeom<T>& g, const UfCtx<T>& C, const T* v, bool
     pair_uf<T, false>(gi, C, v[0], v[1], -v[2], true, RMB_FMA(g.Rz, g.Rz, rxy2), rxy2, ux, uy, uz);
   }
   if (BLOCK == UT || BLOCK == UF_UT) {
-    PairGeom<T> gt = g;
-    gt.h = ht;
     const T* t = (BLOCK == UF_UT) ? v + 3 : v;   // fused: second vector is torque / a
-    pair_ut<T, WALL>(gt, t[0], t[1], t[2], any_near, r2, rxy2, ux, uy, uz);
+    pair_ut<T, WALL, ZOPEN>(g, C, t[0], t[1], t[2], any_near, r2, rxy2, ux, uy, uz);
   }
 }
 

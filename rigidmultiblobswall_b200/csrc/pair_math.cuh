@@ -106,7 +106,8 @@ struct PairGeom {
 template <typename T>
 struct UfCtx {
   T c13, c23, cm53, cm73, c103, c43;   // 1/3, 2/3, -5/3, -7/3, 10/3, 4/3
-  T ht, ht2, ht4;                      // target height h_i and its multiples (wall form)
+  T k1, k2, k12, km20, km10, km3, khalf;   // 1, 2, 12, -20, -10, -3, 1/2 (second literal of two-literal FMAs)
+  T ht, ht2, ht4, ht6;                 // target height h_i and its multiples (wall form)
 };
 
 template <typename T>
@@ -115,13 +116,15 @@ RMB_HOST_DEVICE UfCtx<T> make_uf_ctx(T ht)
   UfCtx<T> C;
   C.c13 = T(1.0 / 3.0); C.c23 = T(2.0 / 3.0); C.cm53 = T(-5.0 / 3.0); C.cm73 = T(-7.0 / 3.0);
   C.c103 = T(10.0 / 3.0); C.c43 = T(4.0 / 3.0);
-  C.ht = ht; C.ht2 = T(2.0) * ht; C.ht4 = T(4.0) * ht;
+  C.k1 = T(1.0); C.k2 = T(2.0); C.k12 = T(12.0); C.km20 = T(-20.0); C.km10 = T(-10.0); C.km3 = T(-3.0);
+  C.khalf = T(0.5);
+  C.ht = ht; C.ht2 = T(2.0) * ht; C.ht4 = T(4.0) * ht; C.ht6 = T(6.0) * ht;
   return C;
 }
 template <typename T>
 RMB_HD void set_target_height(UfCtx<T>& C, T ht)
 {
-  C.ht = ht; C.ht2 = T(2.0) * ht; C.ht4 = T(4.0) * ht;
+  C.ht = ht; C.ht2 = T(2.0) * ht; C.ht4 = T(4.0) * ht; C.ht6 = T(6.0) * ht;
 }
 
 template <typename T, bool WALL, bool ZOPEN = false>
@@ -196,13 +199,24 @@ RMB_HD void self_uf(T h, T fx, T fy, T fz, T& ux, T& uy, T& uz)
 
 // -------------------------------------------------------------- UT / WF ----
 // Free-space translation-rotation coupling (mobility_numba.py:611-648,
-// :1001-1035): antisymmetric, M v = k (v x r) with k = 1/r^3 (r >= 2) or
+// :1001-1035): antisymmetric, M v = kf (v x r) with kf = 1/r^3 (r >= 2) or
 // (1 - 3r/8)/2 (r < 2).
 // Wall corrections: WF (:1037-1066) uses e = (rx,ry,Rz)/|R| and the SOURCE
 // height; UT (:648-679) is the transposed call: e = (-rx,-ry,Rz)/|R| and the
-// TARGET height.  With g = h/|R| (= h_hat*ez):
-//   f1 = q^2, f2 = 12 g ez q^2 + 2(1-10ez^2) q^4,
-//   f3 = -6 g q^2 + 10 ez q^4, f4 = -2 g q^2 + 2 ez q^4
+// TARGET height.  fact1 = q^2, fact2 = 12 h_hat ez^2 q^2 + 2(1-10 ez^2) q^4,
+// fact3 = -2 ez (3 h_hat q^2 - 5 q^4), fact4 = -2 ez (h_hat q^2 - q^4).
+// In unnormalised form (q = 1/|R|, t = q^2, Zt = Rz t, k = Rz^2 t, h the
+// height the reference uses) every entry is q^3 times a polynomial:
+//   fact3 q^2        = q^3 t (10 Zt - 6h)
+//   fact1 ez + fact4 = q^3 c14,  c14 = Rz - 2h + 2 Zt
+//   fact1 + fact2    = q^2 c12,  c12 = 1 + 2t + 12 h Zt - 20 k t
+//   fact3 ez + fact1 + fact2 = q^2 c12', c12' = 1 + 2t + 6 h Zt - 10 k t
+// and free + wall collapse to (f = force, tq = torque, cz = (r x v)_z):
+//   WF: w_x = f_y P1 - r_y P2, w_y = -f_x P1 + r_x P2, w_z = (kf - q^3)(r_y f_x - r_x f_y)
+//       P1 = kf r_z - q^3 c14,  P2 = kf f_z - q^3 [t (10 Zt - 6h)(R.f) + c12 f_z]
+//   UT: u_x = t_y P1 - r_y t_z (kf - q^3) - q^3 E r_x,  u_y = -t_x P1 + r_x t_z (kf - q^3) - q^3 E r_y,
+//       u_z = cz (q^3 c12' - kf),  P1 = kf r_z + q^3 c14,  E = t (10 Zt - 6h) cz,  cz = r_x t_y - r_y t_x
+// 50 (WF) / 47 (UT) FP64 instructions per far pair, was 70 / 68 in e-vector form.
 template <typename T>
 RMB_HD T coupling_k(T r2, bool any_near)
 {
@@ -215,64 +229,64 @@ RMB_HD T coupling_k(T r2, bool any_near)
   return k;
 }
 
-template <typename T>
-struct CouplingWall {
-  T ex, ey, ez, f1, f12, f3, f1ez4;  // f12 = f1+f2, f1ez4 = f1*ez + f4
-};
-
-template <typename T>
-RMB_HD CouplingWall<T> coupling_wall(T rx, T ry, T Rz, T h, T rxy2)
+// rotation from force: w_i += WF_ij f_j   (units 1/(8 pi eta a^2)); p.h = SOURCE height
+template <typename T, bool WALL, bool ZOPEN = false>
+RMB_HD void pair_wf(const PairGeom<T>& p, const UfCtx<T>& C, T fx, T fy, T fz, bool any_near, T r2, T rxy2, T& ux,
+                    T& uy, T& uz)
 {
-  CouplingWall<T> c;
-  const T q = rsqrt_full(RMB_FMA(Rz, Rz, rxy2));
-  const T q2 = q * q;
-  const T q4 = q2 * q2;
-  c.ex = rx * q; c.ey = ry * q; c.ez = Rz * q;
-  const T g = h * q;
-  const T ez2 = c.ez * c.ez;
-  c.f1 = q2;
-  const T f2 = RMB_FMA(T(12.0) * g * c.ez, q2, RMB_FMA(T(-20.0), ez2, T(2.0)) * q4);
-  c.f3 = RMB_FMA(T(-6.0) * g, q2, T(10.0) * c.ez * q4);
-  const T f4 = RMB_FMA(T(-2.0) * g, q2, T(2.0) * c.ez * q4);
-  c.f12 = c.f1 + f2;
-  c.f1ez4 = RMB_FMA(c.f1, c.ez, f4);
-  return c;
-}
-
-// rotation from force: w_i += WF_ij f_j   (units 1/(8 pi eta a^2))
-template <typename T, bool WALL>
-RMB_HD void pair_wf(const PairGeom<T>& p, T fx, T fy, T fz, bool any_near, T r2, T rxy2, T& ux, T& uy, T& uz)
-{
-  const T k = coupling_k(r2, any_near);
-  ux = RMB_FMA(k, RMB_FMA(p.rz, fy, -(p.ry * fz)), ux);
-  uy = RMB_FMA(k, RMB_FMA(p.rx, fz, -(p.rz * fx)), uy);
-  uz = RMB_FMA(k, RMB_FMA(p.ry, fx, -(p.rx * fy)), uz);
-  if (WALL) {
-    const CouplingWall<T> c = coupling_wall(p.rx, p.ry, p.Rz, p.h, rxy2);
-    const T ef = RMB_FMA(c.ez, fz, RMB_FMA(c.ey, fy, c.ex * fx));
-    const T t3 = c.f3 * ef;
-    ux += RMB_FMA(t3, c.ey, RMB_FMA(c.f12 * c.ey, fz, -(c.f1ez4 * fy)));
-    uy += -RMB_FMA(t3, c.ex, RMB_FMA(c.f12 * c.ex, fz, -(c.f1ez4 * fx)));
-    uz = RMB_FMA(c.f1, RMB_FMA(c.ex, fy, -(c.ey * fx)), uz);
+  const T kf = coupling_k(r2, any_near);
+  if (!WALL) {
+    ux = RMB_FMA(kf, RMB_FMA(p.rz, fy, -(p.ry * fz)), ux);
+    uy = RMB_FMA(kf, RMB_FMA(p.rx, fz, -(p.rz * fx)), uy);
+    uz = RMB_FMA(kf, RMB_FMA(p.ry, fx, -(p.rx * fy)), uz);
+  } else {
+    const T q = rsqrt_full(ZOPEN ? RMB_FMA(C.ht4, p.h, r2) : RMB_FMA(p.Rz, p.Rz, rxy2));
+    const T t = q * q;
+    const T Zt = p.Rz * t;
+    const T q3 = q * t;
+    const T k = p.Rz * Zt;
+    const T Rf = RMB_FMA(p.Rz, fz, RMB_FMA(p.ry, fy, p.rx * fx));
+    const T e10 = RMB_FMA(T(10.0), Zt, T(-6.0) * p.h);
+    const T E = (e10 * t) * Rf;
+    const T c14 = RMB_FMA(T(2.0), Zt, ZOPEN ? p.rz : RMB_FMA(T(-2.0), p.h, p.Rz));   // Rz - 2 h_j = z_i - z_j
+    const T c12 = RMB_FMA(RMB_FMA(C.km20, k, C.k2), t, RMB_FMA(C.k12, p.h * Zt, C.k1));
+    const T D = RMB_FMA(c12, fz, E);
+    const T P1 = RMB_FMA(-q3, c14, kf * p.rz);
+    const T P2 = RMB_FMA(-q3, D, kf * fz);
+    const T cz = RMB_FMA(p.ry, fx, -(p.rx * fy));
+    ux = RMB_FMA(fy, P1, ux); ux = RMB_FMA(-p.ry, P2, ux);
+    uy = RMB_FMA(-fx, P1, uy); uy = RMB_FMA(p.rx, P2, uy);
+    uz = RMB_FMA(kf - q3, cz, uz);
   }
 }
 
-// translation from torque: u_i += UT_ij t_j   (units 1/(8 pi eta a^2));
-// p.h must hold the TARGET height here.
-template <typename T, bool WALL>
-RMB_HD void pair_ut(const PairGeom<T>& p, T tx, T ty, T tz, bool any_near, T r2, T rxy2, T& ux, T& uy, T& uz)
+// translation from torque: u_i += UT_ij t_j   (units 1/(8 pi eta a^2)); the wall term uses the
+// TARGET height C.ht (transposed call, :651); p.h (source height) only enters |R|^2.
+template <typename T, bool WALL, bool ZOPEN = false>
+RMB_HD void pair_ut(const PairGeom<T>& p, const UfCtx<T>& C, T tx, T ty, T tz, bool any_near, T r2, T rxy2, T& ux,
+                    T& uy, T& uz)
 {
-  const T k = coupling_k(r2, any_near);
-  ux = RMB_FMA(k, RMB_FMA(p.rz, ty, -(p.ry * tz)), ux);
-  uy = RMB_FMA(k, RMB_FMA(p.rx, tz, -(p.rz * tx)), uy);
-  uz = RMB_FMA(k, RMB_FMA(p.ry, tx, -(p.rx * ty)), uz);
-  if (WALL) {
-    const CouplingWall<T> c = coupling_wall(-p.rx, -p.ry, p.Rz, p.h, rxy2);
-    const T cc = RMB_FMA(c.ey, tx, -(c.ex * ty));
-    const T t3 = c.f3 * cc;
-    ux += RMB_FMA(t3, c.ex, RMB_FMA(c.f1ez4, ty, -(c.f1 * c.ey) * tz));
-    uy += RMB_FMA(t3, c.ey, RMB_FMA(c.f1 * c.ex, tz, -(c.f1ez4 * tx)));
-    uz = RMB_FMA(RMB_FMA(c.f3, c.ez, c.f12), cc, uz);
+  const T kf = coupling_k(r2, any_near);
+  if (!WALL) {
+    ux = RMB_FMA(kf, RMB_FMA(p.rz, ty, -(p.ry * tz)), ux);
+    uy = RMB_FMA(kf, RMB_FMA(p.rx, tz, -(p.rz * tx)), uy);
+    uz = RMB_FMA(kf, RMB_FMA(p.ry, tx, -(p.rx * ty)), uz);
+  } else {
+    const T q = rsqrt_full(ZOPEN ? RMB_FMA(C.ht4, p.h, r2) : RMB_FMA(p.Rz, p.Rz, rxy2));
+    const T t = q * q;
+    const T Zt = p.Rz * t;
+    const T q3 = q * t;
+    const T k = p.Rz * Zt;
+    const T cz = RMB_FMA(p.rx, ty, -(p.ry * tx));
+    const T E = (RMB_FMA(T(10.0), Zt, -C.ht6) * t) * cz;
+    const T c14 = RMB_FMA(T(2.0), Zt, ZOPEN ? -p.rz : p.Rz - C.ht2);                  // Rz - 2 h_i = z_j - z_i
+    const T c12 = RMB_FMA(RMB_FMA(C.km10, k, C.k2), t, RMB_FMA(C.ht6, Zt, C.k1));
+    const T P1 = RMB_FMA(q3, c14, kf * p.rz);
+    const T dt = (kf - q3) * tz;
+    const T qE = q3 * E;
+    ux = RMB_FMA(ty, P1, ux); ux = RMB_FMA(-p.ry, dt, ux); ux = RMB_FMA(-qE, p.rx, ux);
+    uy = RMB_FMA(-tx, P1, uy); uy = RMB_FMA(p.rx, dt, uy); uy = RMB_FMA(-qE, p.ry, uy);
+    uz = RMB_FMA(cz, RMB_FMA(q3, c12, -kf), uz);
   }
 }
 
@@ -298,13 +312,15 @@ RMB_HD void self_ut(T h, T tx, T ty, T& ux, T& uy)
 // Free space (:1252-1290): far (r >= 2) (-1/2 I + 3/2 rr/r^2)/r^3; near
 // (1 - 27r/32 + 5r^3/64) I + (9/(32r) - 3r/64) rr.  Wall (:1302-1321):
 // fact1 = (1-6ez^2)q^3/2, fact2 = -3q^3/2, fact3 = 3 q^3 ez, fact4 = 3 q^3.
-template <typename T, bool WALL>
-RMB_HD void pair_wt(const PairGeom<T>& p, T tx, T ty, T tz, bool any_near, T r2, T rxy2, T& ux, T& uy, T& uz)
+template <typename T, bool WALL, bool ZOPEN = false>
+RMB_HD void pair_wt(const PairGeom<T>& p, const UfCtx<T>& C, T tx, T ty, T tz, bool any_near, T r2, T rxy2, T& ux,
+                    T& uy, T& uz)
 {
   const T invr = rsqrt_full(r2);
   const T invr2 = invr * invr;
   const T invr3 = invr2 * invr;
-  const T rt = RMB_FMA(p.rz, tz, RMB_FMA(p.ry, ty, p.rx * tx));
+  const T s = RMB_FMA(p.ry, ty, p.rx * tx);
+  const T rt = RMB_FMA(p.rz, tz, s);
   T A = T(-0.5) * invr3;
   T B = (T(1.5) * invr2) * invr3 * rt;
   if (any_near) {
@@ -315,21 +331,27 @@ RMB_HD void pair_wt(const PairGeom<T>& p, T tx, T ty, T tz, bool any_near, T r2,
     A = near ? An : A;
     B = near ? Bn : B;
   }
-  ux = RMB_FMA(A, tx, ux); uy = RMB_FMA(A, ty, uy); uz = RMB_FMA(A, tz, uz);
-  ux = RMB_FMA(B, p.rx, ux); uy = RMB_FMA(B, p.ry, uy); uz = RMB_FMA(B, p.rz, uz);
-  if (WALL) {
-    const T q = rsqrt_full(RMB_FMA(p.Rz, p.Rz, rxy2));
-    const T q3 = q * q * q;
-    const T ex = p.rx * q, ey = p.ry * q, ez = p.Rz * q;
-    const T f1 = RMB_FMA(T(-3.0), ez * ez, T(0.5)) * q3;
-    const T f2 = T(-1.5) * q3;
-    const T f4 = T(3.0) * q3;
-    const T et = RMB_FMA(ez, tz, RMB_FMA(ey, ty, ex * tx));
-    const T cc = RMB_FMA(ex, ty, -(ey * tx));
-    const T f2et = f2 * et;
-    ux += RMB_FMA(f1, tx, RMB_FMA(f2et, ex, -(f4 * ey) * cc));
-    uy += RMB_FMA(f1, ty, RMB_FMA(f2et, ey, (f4 * ex) * cc));
-    uz += RMB_FMA(f1, tz, RMB_FMA(f2, ez, f4 * ez) * et);   // (f2 ez + f3), f3 = f4 ez
+  if (!WALL) {
+    ux = RMB_FMA(A, tx, ux); uy = RMB_FMA(A, ty, uy); uz = RMB_FMA(A, tz, uz);
+    ux = RMB_FMA(B, p.rx, ux); uy = RMB_FMA(B, p.ry, uy); uz = RMB_FMA(B, p.rz, uz);
+  } else {
+    // unnormalised wall term (cz = r_x t_y - r_y t_x, Rt = R.t, q5 = q^5):
+    //   u_x += q^3 (1/2 - 3k) t_x - 3/2 q5 Rt r_x - 3 q5 cz r_y      u_y likewise with (+3 q5 cz r_x)
+    //   u_z += q^3 (1/2 - 3k) t_z + 3/2 q5 Rt Rz
+    const T q = rsqrt_full(ZOPEN ? RMB_FMA(C.ht4, p.h, r2) : RMB_FMA(p.Rz, p.Rz, rxy2));
+    const T t = q * q;
+    const T q3 = q * t;
+    const T k = (p.Rz * p.Rz) * t;
+    const T q5 = q3 * t;
+    const T Rt = RMB_FMA(p.Rz, tz, s);
+    const T cz = RMB_FMA(p.rx, ty, -(p.ry * tx));
+    const T Aa = RMB_FMA(RMB_FMA(C.km3, k, C.khalf), q3, A);
+    const T m1 = (T(-1.5) * q5) * Rt;
+    const T m2 = (T(3.0) * q5) * cz;
+    const T Bm = B + m1;
+    ux = RMB_FMA(Aa, tx, ux); ux = RMB_FMA(Bm, p.rx, ux); ux = RMB_FMA(-m2, p.ry, ux);
+    uy = RMB_FMA(Aa, ty, uy); uy = RMB_FMA(Bm, p.ry, uy); uy = RMB_FMA(m2, p.rx, uy);
+    uz = RMB_FMA(Aa, tz, uz); uz = RMB_FMA(B, p.rz, uz); uz = RMB_FMA(-m1, p.Rz, uz);
   }
 }
 
