@@ -65,6 +65,7 @@ struct StArgs {
   T* partial;            // [n_split][n_trg][3] when n_split > 1
   double* out;           // [n_trg][3]
   double norm;           // 1/(8 pi eta)
+  StConsts<T> K;         // literals of st_math.cuh (constant bank)
 };
 
 template <typename T, int WALLMODE, bool PERIODIC, bool TMA>
@@ -132,7 +133,7 @@ __global__ void __launch_bounds__(TPB) st_kernel(const __grid_constant__ StArgs<
         if (A.P.per[1]) ry = wrap_shift(ry, A.P.L[1], A.P.invL[1], sy);
         if (A.P.per[2]) rz = wrap_shift(rz, A.P.L[2], A.P.invL[2], sz);
       }
-      pair_st<T, WALLMODE>(t, rx, ry, rz, t.z + w[2], w[2], w[6], w[7], w[3], w[4], w[5], ux, uy, uz);
+      pair_st<T, WALLMODE>(A.K, t, rx, ry, rz, t.z + w[2], w[2], w[6], w[7], w[3], w[4], w[5], ux, uy, uz);
     }
     __syncthreads();
     if (TMA) stage ^= 1;
@@ -235,6 +236,7 @@ int launch(const StCall& c)
   A.partial = reinterpret_cast<T*>(c.ws + p.off_partial);
   A.out = c.out;
   A.norm = 1.0 / (8.0 * 3.14159265358979323846 * c.eta);
+  A.K = make_st_consts<T>();
   const dim3 grid((unsigned)p.tgt_blocks, (unsigned)p.n_split);
   if (c.flags & RMB_NO_TMA) st_kernel<T, WALLMODE, PERIODIC, false><<<grid, TPB, 0, c.stream>>>(A);
   else st_kernel<T, WALLMODE, PERIODIC, true><<<grid, TPB, 0, c.stream>>>(A);

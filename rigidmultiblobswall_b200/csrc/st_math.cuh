@@ -38,6 +38,22 @@ RMB_HD double min_t(double a, double b) { return fmin(a, b); }
 RMB_HD float min_t(float a, float b) { return fminf(a, b); }
 #endif
 
+// Literals with a non-zero low word (and the second literal of two-literal FMAs): host-filled, read from
+// the kernel's constant bank so that the pair loop holds no constant-materialising moves.
+template <typename T>
+struct StConsts {
+  T c13, c23, c43, c103, cm23, cm703, c203, cm132, k2, k3, k6, k10, khalf;
+};
+template <typename T>
+RMB_HOST_DEVICE StConsts<T> make_st_consts()
+{
+  StConsts<T> K;
+  K.c13 = T(1.0 / 3.0); K.c23 = T(2.0 / 3.0); K.c43 = T(4.0 / 3.0); K.c103 = T(10.0 / 3.0); K.cm23 = T(-2.0 / 3.0);
+  K.cm703 = T(-70.0 / 3.0); K.c203 = T(20.0 / 3.0); K.cm132 = T(-1.0 / 32.0);
+  K.k2 = T(2.0); K.k3 = T(3.0); K.k6 = T(6.0); K.k10 = T(10.0); K.khalf = T(0.5);
+  return K;
+}
+
 // u += C1 f + C2 (r.f) r with (mobility_numba.py:1552-1566)
 //   r > a+b      : C1 = (1 + S/(3r^2))/r,  C2 = (1 - S/r^2)/r^3,  S = a^2+b^2
 //   |b-a| < r    : C1 = [ (a+b)/2 - (D+3r^2)^2/(32 r^3) ] 4/(3ab),  D = (b-a)^2
@@ -45,25 +61,25 @@ RMB_HD float min_t(float a, float b) { return fminf(a, b); }
 //   r <= |b-a|   : C1 = 4/(3 max(a,b)), C2 = 0
 // sab2 = (a+b)^2; any_near = warp-uniform "some lane may have r2 <= sab2".
 template <typename T>
-RMB_HD void rpy_radii(T rx, T ry, T rz, T r2, T a, T ia, T b, T ib, T S, T sab2, bool any_near, T fx, T fy, T fz,
-                      T& ux, T& uy, T& uz)
+RMB_HD void rpy_radii(const StConsts<T>& K, T rx, T ry, T rz, T r2, T a, T ia, T b, T ib, T S, T sab2, bool any_near,
+                      T fx, T fy, T fz, T& ux, T& uy, T& uz)
 {
   const T invr = rsqrt_full(r2);
   const T invr2 = invr * invr;
   const T invr3 = invr2 * invr;
-  T C1 = RMB_FMA(T(1.0 / 3.0) * S, invr3, invr);
+  T C1 = RMB_FMA(K.c13 * S, invr3, invr);
   T C2 = RMB_FMA(-(S * invr2), invr3, invr3);
   if (any_near) {
     const T d = b - a;
     const T D = d * d;
     const T iab = ia * ib;
-    const T g = RMB_FMA(T(3.0), r2, D);
-    const T C1n = RMB_FMA(T(-1.0 / 32.0) * (g * g), invr3, T(0.5) * (a + b)) * (T(4.0 / 3.0) * iab);
+    const T g = RMB_FMA(K.k3, r2, D);
+    const T C1n = RMB_FMA(K.cm132 * (g * g), invr3, K.khalf * (a + b)) * (K.c43 * iab);
     const T e = D - r2;
     const T C2n = (T(0.125) * iab) * (e * e) * (invr3 * invr2);
     const bool far = r2 > sab2;
     const bool inside = !(r2 > D);
-    C1 = far ? C1 : (inside ? T(4.0 / 3.0) * min_t(ia, ib) : C1n);
+    C1 = far ? C1 : (inside ? K.c43 * min_t(ia, ib) : C1n);
     C2 = far ? C2 : (inside ? T(0) : C2n);
   }
   const T rf = RMB_FMA(rz, fz, RMB_FMA(ry, fy, rx * fx));
@@ -84,7 +100,8 @@ RMB_HD void rpy_radii(T rx, T ry, T rz, T r2, T a, T ia, T b, T ib, T S, T sab2,
 //   ep = -2q - q^3 [ 2S/3 + (4P/3) t ]
 // S = a^2+b^2, P = a^2 b^2, W = a^2 y3 + b^2 x3, k = Z^2 t.
 template <typename T>
-RMB_HD void wall_radii(T rx, T ry, T Z, T rxy2, T x3, T y3, T a2, T b2, T S, T fx, T fy, T fz, T& ux, T& uy, T& uz)
+RMB_HD void wall_radii(const StConsts<T>& K, T rx, T ry, T Z, T rxy2, T x3, T y3, T a2, T b2, T S, T fx, T fy, T fz,
+                       T& ux, T& uy, T& uz)
 {
   const T q = rsqrt_full(RMB_FMA(Z, Z, rxy2));
   const T t = q * q;
@@ -97,18 +114,18 @@ RMB_HD void wall_radii(T rx, T ry, T Z, T rxy2, T x3, T y3, T a2, T b2, T S, T f
   const T dab = a2 - b2;
   const T Pt = P * t;
   const T ZW = Zt * W;
-  T al = RMB_FMA(T(10.0 / 3.0) * Pt, k, T(-2.0 / 3.0) * Pt);          // (2P/3) t (5k - 1)
+  T al = RMB_FMA(K.c103 * Pt, k, K.cm23 * Pt);          // (2P/3) t (5k - 1)
   al = RMB_FMA(T(-2.0), ZW, al);
-  al += RMB_FMA(T(2.0), xy, T(1.0 / 3.0) * S);
+  al += RMB_FMA(K.k2, xy, K.c13 * S);
   al = RMB_FMA(q3, al, q);
-  T be = RMB_FMA(T(-70.0 / 3.0) * Pt, k, T(10.0 / 3.0) * Pt);         // (10P/3) t (1 - 7k)
-  be = RMB_FMA(T(10.0), ZW, be);
-  be -= RMB_FMA(T(6.0), xy, S);
+  T be = RMB_FMA(K.cm703 * Pt, k, K.c103 * Pt);         // (10P/3) t (1 - 7k)
+  be = RMB_FMA(K.k10, ZW, be);
+  be -= RMB_FMA(K.k6, xy, S);
   be = RMB_FMA(be, t, T(1.0));
-  const T c20 = T(20.0 / 3.0) * Pt * Zt;                              // (20P/3) Z t^2
+  const T c20 = K.c203 * Pt * Zt;                              // (20P/3) Z t^2
   const T ga = RMB_FMA(x3 + x3, RMB_FMA(dab, t, T(-1.0)), c20);
   const T de = RMB_FMA(y3 + y3, RMB_FMA(-dab, t, T(-1.0)), c20);
-  const T ep = -RMB_FMA(q3, RMB_FMA(T(4.0 / 3.0), Pt, T(2.0 / 3.0) * S), q + q);
+  const T ep = -RMB_FMA(q3, RMB_FMA(K.c43, Pt, K.c23 * S), q + q);
   const T Rf = RMB_FMA(Z, fz, -RMB_FMA(ry, fy, rx * fx));
   const T cR = RMB_FMA(be, Rf, ga * fz) * q3;
   const T cz = RMB_FMA(de * q3, Rf, ep * fz);
@@ -159,7 +176,7 @@ RMB_HD double st_target(bool wall, double x, double y, double z, double radius, 
 // One pair.  (rx, ry, rz) after the image wrap, Z = z_i + z_j (no wrap, :1583),
 // y3 = source height, b / ib = source radius and its reciprocal.
 template <typename T, int WALLMODE>
-RMB_HD void pair_st(const StTarget<T>& t, T rx, T ry, T rz, T Z, T y3, T b, T ib, T fx, T fy, T fz, T& ux, T& uy,
+RMB_HD void pair_st(const StConsts<T>& K, const StTarget<T>& t, T rx, T ry, T rz, T Z, T y3, T b, T ib, T fx, T fy, T fz, T& ux, T& uy,
                     T& uz)
 {
   const T rxy2 = RMB_FMA(ry, ry, rx * rx);
@@ -168,11 +185,11 @@ RMB_HD void pair_st(const StTarget<T>& t, T rx, T ry, T rz, T Z, T y3, T b, T ib
   const T S = t.a2 + b2;
   const T sab = t.a + b;
   const T sab2 = sab * sab;
-  rpy_radii<T>(rx, ry, rz, r2, t.a, t.ia, b, ib, S, sab2, warp_any(maybe_le(r2, sab2)), fx, fy, fz, ux, uy, uz);
-  if (WALLMODE == ST_WALL) wall_radii<T>(rx, ry, Z, rxy2, t.z, y3, t.a2, b2, S, fx, fy, fz, ux, uy, uz);
+  rpy_radii<T>(K, rx, ry, rz, r2, t.a, t.ia, b, ib, S, sab2, warp_any(maybe_le(r2, sab2)), fx, fy, fz, ux, uy, uz);
+  if (WALLMODE == ST_WALL) wall_radii<T>(K, rx, ry, Z, rxy2, t.z, y3, t.a2, b2, S, fx, fy, fz, ux, uy, uz);
   if (WALLMODE == ST_FREE_SURFACE) {
     const T R2 = RMB_FMA(Z, Z, rxy2);
-    rpy_radii<T>(rx, ry, Z, R2, t.a, t.ia, b, ib, S, sab2, warp_any(maybe_le(R2, sab2)), fx, fy, -fz, ux, uy, uz);
+    rpy_radii<T>(K, rx, ry, Z, R2, t.a, t.ia, b, ib, S, sab2, warp_any(maybe_le(R2, sab2)), fx, fy, -fz, ux, uy, uz);
   }
 }
 

@@ -132,7 +132,7 @@ static void run_st(long nt, long ns, const double* trg, const double* src, const
         if (P.per[0]) rx = wrap_shift(rx, P.L[0], P.invL[0], sx);
         if (P.per[1]) ry = wrap_shift(ry, P.L[1], P.invL[1], sy);
         if (P.per[2]) rz = wrap_shift(rz, P.L[2], P.invL[2], sz);
-        pair_st<T, WALLMODE>(t, rx, ry, rz, t.z + rec[j].z, rec[j].z, rec[j].b, rec[j].ib, rec[j].fx, rec[j].fy,
+        pair_st<T, WALLMODE>(make_st_consts<T>(), t, rx, ry, rz, t.z + rec[j].z, rec[j].z, rec[j].b, rec[j].ib, rec[j].fx, rec[j].fy,
                              rec[j].fz, ux, uy, uz);
       }
     }
