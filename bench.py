@@ -22,6 +22,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 FLOP_PER_PAIR = 200.0   # algorithmic flop of one single-wall UF pair as the oracle writes it
+FP64_INSTR_PER_PAIR = 66  # FP64-pipe instructions the kernel executes per far pair (SASS count)
 METRIC = "single-wall fp64 Mf pair-interactions/s at N=1M"
 
 
@@ -269,7 +270,13 @@ def run_b200(args):
         # step's other launches (L2 flush memset, prepare_kernel) are < 0.1% of it
         launch_ms = ms / args.steps
         achieved = (float(cnt) * n * FLOP_PER_PAIR) / (launch_ms * 1e-3) / 1e12
-        plan_launches = 2   # prepare_kernel + mf_kernel (n_split == 1 at this size: no finish_kernel)
+        plan_launches = int(_lib.load().rmb_launches_per_product(mb.UF, mb.FP64, cnt, n, None))
+        sms = _lib.load().rmb_device_sm_count()
+        nominal = sms * 64 * 2 * (clocks.get("sm_mhz") or 1965.0) * 1e6 / 1e12   # 64 FP64 FMA lanes / clk / SM
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "flagship_traffic.json")
+        if os.path.exists(tpath) and n == 1000000 and world == 1:
+            traffic = json.load(open(tpath))["dram_bytes_total"]
         line = {
             "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
@@ -278,10 +285,17 @@ def run_b200(args):
                        "sharding": "targets by rank, sources replicated, NCCL all-gather of force slices per step"
                        if world > 1 else "single GPU",
                        "l2": "flushed between iterations (256 MiB memset inside the timed region)"},
-            "roofline": {"bound": "fp64_fma", "achieved": achieved, "peak": peak_flops / 1e12, "unit": "TFLOP/s",
-                         "frac": achieved / (peak_flops / 1e12), "traffic": None,
+            "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak_flops / 1e12, "unit": "TFLOP/s",
+                         "frac": achieved / (peak_flops / 1e12), "traffic": traffic,
                          "flop_per_pair": FLOP_PER_PAIR,
-                         "peak_source": "rmb_fma_peak (FP64 FMA probe, measured in this run on this GPU)"},
+                         "peak_source": "rmb_fma_peak (FP64 FMA probe, measured in this run on this GPU)",
+                         "note": "achieved counts the reference's 200 flop per pair (SURVEY 8d); the kernel executes "
+                                 "fp64_instr_per_pair FP64-pipe instructions per pair, pipe_frac = those lanes/s over "
+                                 "the nominal issue rate (SMs x 64 lanes x SM clock); traffic = DRAM bytes of one launch "
+                                 "from ncu (profiles/flagship_traffic.json), algorithmic bytes are 72 B per blob",
+                         "fp64_instr_per_pair": FP64_INSTR_PER_PAIR,
+                         "pipe_frac": value / world * FP64_INSTR_PER_PAIR * 2 / 1e12 / nominal,
+                         "nominal_peak": nominal},
             "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": "pairs/s", "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": int(world * 2 * 24 * n), "d2h_bytes_per_step": int(24 * n)},

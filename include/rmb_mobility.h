@@ -75,6 +75,9 @@ int rmb_device_sm_count(void);
  */
 size_t rmb_workspace_bytes(int block, int precision, long n_targets, long n_sources, const double *L);
 
+/* Kernels one rmb_mobility_product() call launches for this problem (2, or 3 when sources are split). */
+int rmb_launches_per_product(int block, int precision, long n_targets, long n_sources, const double *L);
+
 /*
  * out[0:3*n_targets] = rows [target_offset, target_offset + n_targets) of
  *     B * M(r_eff) * (B * vec)            (single wall)

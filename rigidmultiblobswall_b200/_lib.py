@@ -34,6 +34,9 @@ def load():
     lib.rmb_workspace_bytes.restype = ctypes.c_size_t
     lib.rmb_workspace_bytes.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_long, ctypes.c_long,
                                         ctypes.POINTER(ctypes.c_double)]
+    lib.rmb_launches_per_product.restype = ctypes.c_int
+    lib.rmb_launches_per_product.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_long, ctypes.c_long,
+                                             ctypes.POINTER(ctypes.c_double)]
     lib.rmb_mobility_product.restype = ctypes.c_int
     lib.rmb_mobility_product.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                          ctypes.c_long, ctypes.c_long, ctypes.c_long,

@@ -35,7 +35,7 @@ namespace {
 #define RMB_UNROLL 4      // source-loop unroll of the open-boundary kernels
 #endif
 #ifndef RMB_UNROLL_PER
-#define RMB_UNROLL_PER 2  // same for the pseudo-periodic kernels (more live registers per pair)
+#define RMB_UNROLL_PER 1  // image-box loop of the pseudo-periodic kernels (measured best: 1)
 #endif
 #ifndef RMB_MINB
 #define RMB_MINB 1
@@ -456,6 +456,14 @@ size_t rmb_workspace_bytes(int block, int precision, long n_targets, long n_sour
   if (block < 0 || block > RMB_UF_UT || n_targets < 0 || n_sources < 0) return 0;
   if (make_plan(block, precision, n_targets, n_sources, L, p) != 0) return 0;
   return p.total;
+}
+
+int rmb_launches_per_product(int block, int precision, long n_targets, long n_sources, const double* L)
+{
+  Plan p;
+  if (block < 0 || block > RMB_UF_UT || n_targets <= 0 || n_sources <= 0) return 0;
+  if (make_plan(block, precision, n_targets, n_sources, L, p) != 0) return 0;
+  return 2 + (p.n_split > 1 ? 1 : 0);   // prepare_kernel + mf_kernel (+ finish_kernel when sources are split)
 }
 
 int rmb_mobility_product(int block, int wall, int precision, int flags, long n_targets, long n_sources,
