@@ -182,6 +182,74 @@ RMB_HD void pair_uf(const PairGeom<T>& p, const UfCtx<T>& C, T fx, T fy, T fz, b
   }
 }
 
+// Both directions of one pair at once (single wall, no image wrap): u_i += M_ij f_j AND u_j += M_ji f_i.
+// M_ji is M_ij with r -> -r and the source height h_j -> h_i, so the two evaluations share the geometry, both
+// reciprocal square roots, the free-space coefficients and q, t, k, A_q, X, Y, b2, v, p1, p2, W_v: 44 common FP64
+// instructions + 22 per direction = 88 for two interactions (2 x 66 when evaluated separately).
+//   direction d (force f, source height H, sign s = +1 for i<-j, -1 for j<-i), with S = r_x f_x + r_y f_y:
+//     B_f = b' (S + r_z f_z)              (free space, even in r)
+//     R.f = s S + R_z f_z,   G = p2 (R.f) + 2 p3h f_z,   SZh = p4h (R.f) - 2 p5q f_z
+//     u_xy += A_f f_xy + (B_f + s q^3 G) r_xy,   u_z += A_f f_z + B_f r_z + q^3 (G R_z + 2 SZh)
+// C holds the multiples of h_i (C.ht4 h_j = 4 h_i h_j, C.ht2 h_j = 2 h_i h_j).
+template <typename T, int SIGN>
+RMB_HD void uf_sym_direction(T rx, T ry, T rz, T Rz, T H, const T* f, T bp, T Af, T q3, T p2, T Zt, T vm, T ZtT, T tW,
+                             T* u)
+{
+  const T S = RMB_FMA(ry, f[1], rx * f[0]);
+  const T Bf = bp * RMB_FMA(rz, f[2], S);
+  const T Rf = RMB_FMA(Rz, f[2], SIGN > 0 ? S : -S);
+  const T p3h = RMB_FMA(-Zt, vm, H);
+  const T p4h = H - ZtT;
+  const T p5q = RMB_FMA(H, H, tW);
+  const T fz2 = f[2] + f[2];
+  const T G = RMB_FMA(p2, Rf, p3h * fz2);
+  const T SZh = RMB_FMA(p4h, Rf, -(p5q * fz2));
+  const T Bx = RMB_FMA(SIGN > 0 ? q3 : -q3, G, Bf);
+  u[0] = RMB_FMA(Af, f[0], u[0]); u[1] = RMB_FMA(Af, f[1], u[1]); u[2] = RMB_FMA(Af, f[2], u[2]);
+  u[0] = RMB_FMA(Bx, rx, u[0]); u[1] = RMB_FMA(Bx, ry, u[1]);
+  u[2] = RMB_FMA(Bf, rz, u[2]); u[2] = RMB_FMA(q3, RMB_FMA(G, Rz, SZh + SZh), u[2]);
+}
+
+// (rx, ry, rz) = x_i - x_j, Rz = h_i + h_j (lengths / a); fi, fj: the two forces; BOTH: also update u_j.
+template <typename T, bool BOTH>
+RMB_HD void pair_uf_wall_sym(T rx, T ry, T rz, T Rz, T hi, T hj, const UfCtx<T>& C, const T* fi, const T* fj,
+                             bool any_near, T r2, T* ui, T* uj)
+{
+  const T invr = rsqrt_full(r2);
+  const T invr2 = invr * invr;
+  const T invr3 = invr2 * invr;
+  T A = RMB_FMA(C.c23, invr3, invr);
+  T bp = RMB_FMA(T(-2.0), invr2 * invr3, invr3);       // (1 - 2/r^2) / r^3
+  if (any_near) {
+    const T r = r2 * invr;
+    const T An = RMB_FMA(T(-0.375), r, C.c43);
+    const T bn = T(0.125) * invr;
+    const bool near = lt4(r2);
+    A = near ? An : A;
+    bp = near ? bn : bp;
+  }
+  const T q = rsqrt_full(RMB_FMA(C.ht4, hj, r2));
+  const T t = q * q;
+  const T Aq = RMB_FMA(Rz, Rz, C.c13);
+  const T Zt = Rz * t;
+  const T t2 = t + t;
+  const T k = Rz * Zt;
+  const T q3 = q * t;
+  const T b2 = RMB_FMA(C.ht2, hj, C.c23);
+  const T X = RMB_FMA(C.cm53, k, Aq);
+  const T Y = RMB_FMA(C.cm73, k, Aq);
+  const T p1 = RMB_FMA(RMB_FMA(t2, X, -b2), t, T(-1.0));
+  const T t103 = C.c103 * t;
+  const T v3 = RMB_FMA(-t103, Y, b2);
+  const T p2 = RMB_FMA(v3, T(3.0) * t, T(-1.0));
+  const T vm = RMB_FMA(T(3.0), v3, -t103);
+  const T ZtT = Zt * t103;
+  const T tW = t * RMB_FMA(T(-5.0), k, Aq + C.c13);
+  const T Af = RMB_FMA(q, p1, A);
+  uf_sym_direction<T, 1>(rx, ry, rz, Rz, hj, fj, bp, Af, q3, p2, Zt, vm, ZtT, tW, ui);
+  if (BOTH) uf_sym_direction<T, -1>(rx, ry, rz, Rz, hi, fi, bp, Af, q3, p2, Zt, vm, ZtT, tW, uj);
+}
+
 // Self term of UF (:203-208, :246-252); h = z_i / a (clamped), f = own force.
 template <typename T, bool WALL>
 RMB_HD void self_uf(T h, T fx, T fy, T fz, T& ux, T& uy, T& uz)

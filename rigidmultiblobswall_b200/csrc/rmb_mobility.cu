@@ -79,6 +79,9 @@ __global__ void prepare_kernel(long n, long n_pad, const double* __restrict__ r,
   T* w = reinterpret_cast<T*>(&o);
 #pragma unroll
   for (int k = 0; k < W; k++) w[k] = T(0);
+  // padding = blobs far away from everything with zero force: the kernels that do evaluate them
+  // (uf_sym_kernel) get finite geometry and exactly zero contributions
+  o.x = T(3.0e7 + 64.0 * (double)(j - n)); o.y = T(3.0e7); o.z = T(3.0e7);
   if (j < n) {
     const double inva = 1.0 / a;
     const double s = scaled ? inva : 1.0;
@@ -294,6 +297,153 @@ __global__ void finish_kernel(const MfArgs<T, (BLOCK == UF_UT) ? 2 : 1> A)
   A.out[3 * li + 2] = A.in_plane ? 0.0 : dz * sc;
 }
 
+// ------------------------------------------------ pair-symmetric UF kernel --
+// Single-wall UF, open boundaries, all blobs both targets and sources: every
+// unordered pair is evaluated ONCE and updates both u_i and u_j
+// (pair_uf_wall_sym: 88 FP64 instructions for two interactions instead of 132).
+//
+// Blobs are cut into blocks of 32.  A warp owns one block I (lane l holds blob
+// 32 I + l in registers) and sweeps the blocks J >= I of its source tiles.  In
+// step s of a block, lane l meets j = 32 J + ((l + s) & 31): every lane reads a
+// different record from the shared-memory tile (conflict-free LDS.128), adds
+// M_ij f_j to its own u_i and M_ji f_i to a travelling accumulator that moves
+// one lane per step (3 x SHFL.64), so after 32 steps lane l holds the sum for
+// blob 32 J + l and flushes it with a global RED.  J == I is the diagonal block:
+// steps 1..31, one direction only.  A CTA = 4 warps = a row group of 128 blobs
+// (blockIdx.x, scaled by the rank stride) x a range of source tiles
+// (blockIdx.y); rows are triangular (tiles >= the row's own), long rows first.
+// Sums are accumulated with atomics in acc[n_pad][3]; sym_finish_kernel adds the
+// self term, the normalisation and the damping.
+struct SymArgs {
+  const SrcRec<double, 1>* src;   // n_tiles * TILE records; padding = far-away blobs with zero force
+  double* acc;                    // [n_tiles * TILE][3], zeroed before the launch
+  int n_tiles, n_split;
+  int row_first, row_stride;      // row groups handled by this launch: row_first + blockIdx.x * row_stride
+  UfCtx<double> K;
+};
+
+template <bool TMA>
+__global__ void __launch_bounds__(TPB, 1) uf_sym_kernel(const __grid_constant__ SymArgs A)
+{
+  typedef double T;
+  constexpr int W = 6;
+  constexpr uint32_t TILE_BYTES = TILE * W * sizeof(T);
+  __shared__ alignas(128) T tile[TMA ? STAGES : 1][TILE * W];
+  __shared__ alignas(8) uint64_t full[STAGES];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = A.row_first + blockIdx.x * A.row_stride;   // row group of 128 blobs
+  const long I = (long)g * (TPB / 32) + warp;              // this warp's block of 32
+  const long gi = I * 32 + lane;
+
+  T xi, yi, hi, fi[3];
+  {
+    const SrcRec<T, 1>& me = A.src[gi];
+    xi = me.x; yi = me.y; hi = me.z;
+    fi[0] = me.v[0]; fi[1] = me.v[1]; fi[2] = me.v[2];
+  }
+  UfCtx<T> C = A.K;
+  set_target_height(C, hi);
+
+  // this CTA's part of the row's tiles [g * TPB / TILE, n_tiles)
+  const int t_first = (int)(((long)g * TPB) / TILE);
+  const int len = A.n_tiles - t_first;
+  const int v0 = t_first + (int)(((long)len * blockIdx.y) / A.n_split);
+  const int v1 = t_first + (int)(((long)len * (blockIdx.y + 1)) / A.n_split);
+  const T* srcw = reinterpret_cast<const T*>(A.src);
+
+  if (TMA) {
+    if (tid == 0) {
+#pragma unroll
+      for (int s = 0; s < STAGES; s++) mbar_init(&full[s], 1);
+      fence_barrier_init();
+    }
+    __syncthreads();
+    if (tid == 0 && v0 < v1) {
+      mbar_expect_tx(&full[0], TILE_BYTES);
+      bulk_g2s(tile[0], srcw + (size_t)v0 * TILE * W, TILE_BYTES, &full[0]);
+    }
+  }
+
+  T ui[3] = {0, 0, 0};
+  int stage = 0;
+  uint32_t phases = 0;
+  for (int v = v0; v < v1; v++) {
+    if (TMA) {
+      if (tid == 0 && v + 1 < v1) {
+        mbar_expect_tx(&full[stage ^ 1], TILE_BYTES);
+        bulk_g2s(tile[stage ^ 1], srcw + (size_t)(v + 1) * TILE * W, TILE_BYTES, &full[stage ^ 1]);
+      }
+      mbar_wait(&full[stage], (phases >> stage) & 1u);
+      phases ^= (1u << stage);
+    } else {
+      const T* gsrc = srcw + (size_t)v * TILE * W;
+      for (int k = tid; k < TILE * W; k += TPB) tile[0][k] = gsrc[k];
+      __syncthreads();
+    }
+    const T* tp = tile[TMA ? stage : 0];
+    for (int jb = 0; jb < TILE / 32; jb++) {
+      const long J = (long)v * (TILE / 32) + jb;
+      if (J < I) continue;                         // warp-uniform: that pair of blocks belongs to the other warp
+      const T* blk = tp + jb * 32 * W;
+      if (J == I) {
+        // diagonal block: ordered pairs (l, (l + s) & 31), s = 1..31, one direction
+#pragma unroll 2
+        for (int s = 1; s < 32; s++) {
+          T w[W];
+          load_rec<W>(blk + ((lane + s) & 31) * W, w);
+          const T rx = xi - w[0], ry = yi - w[1], rz = hi - w[2];
+          const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
+          const bool any_near = __any_sync(0xffffffffu, lt4(r2));
+          pair_uf_wall_sym<T, false>(rx, ry, rz, hi + w[2], hi, w[2], C, fi, w + 3, any_near, r2, ui, ui);
+        }
+      } else {
+        T aj[3] = {0, 0, 0};
+        int jl = lane;
+#pragma unroll 2
+        for (int s = 0; s < 32; s++) {
+          T w[W];
+          load_rec<W>(blk + jl * W, w);
+          const T rx = xi - w[0], ry = yi - w[1], rz = hi - w[2];
+          const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
+          const bool any_near = __any_sync(0xffffffffu, lt4(r2));
+          pair_uf_wall_sym<T, true>(rx, ry, rz, hi + w[2], hi, w[2], C, fi, w + 3, any_near, r2, ui, aj);
+          // the accumulator of blob j moves to the lane that meets j next
+          const int from = (lane + 1) & 31;
+          aj[0] = __shfl_sync(0xffffffffu, aj[0], from);
+          aj[1] = __shfl_sync(0xffffffffu, aj[1], from);
+          aj[2] = __shfl_sync(0xffffffffu, aj[2], from);
+          jl = (jl + 1) & 31;
+        }
+        double* a = A.acc + (size_t)(J * 32 + lane) * 3;   // after 32 moves lane l holds blob 32 J + l
+        atomicAdd(a, aj[0]); atomicAdd(a + 1, aj[1]); atomicAdd(a + 2, aj[2]);
+      }
+    }
+    __syncthreads();
+    if (TMA) stage ^= 1;
+  }
+  double* a = A.acc + (size_t)gi * 3;
+  atomicAdd(a, ui[0]); atomicAdd(a + 1, ui[1]); atomicAdd(a + 2, ui[2]);
+}
+
+// out = B (acc + self term) / (8 pi eta a) for the targets [tgt_off, tgt_off + n_tgt)
+__global__ void sym_finish_kernel(const SrcRec<double, 1>* __restrict__ src, const double* __restrict__ acc,
+                                  const double* __restrict__ damp, long tgt_off, long n_tgt, double norm, int in_plane,
+                                  double* __restrict__ out)
+{
+  const long li = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (li >= n_tgt) return;
+  const long gi = tgt_off + li;
+  const SrcRec<double, 1>& me = src[gi];
+  double sv[3] = {me.v[0], me.v[1], me.v[2]};
+  double dx = acc[3 * gi], dy = acc[3 * gi + 1], dz = acc[3 * gi + 2];
+  self_apply<double, UF, true>(me.z, sv, dx, dy, dz);
+  const double sc = norm * damp[gi];
+  out[3 * li] = dx * sc;
+  out[3 * li + 1] = dy * sc;
+  out[3 * li + 2] = in_plane ? 0.0 : dz * sc;
+}
+
 // ---------------------------------------------------------- host dispatch --
 int g_sm_count = 0;
 
@@ -312,7 +462,8 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 struct Plan {
   int n_tiles, n_boxes, n_vt, n_split, vt_per_split, tgt_blocks;
-  size_t rec_bytes, off_damp, off_partial, total;
+  size_t rec_bytes, off_damp, off_partial, off_acc, total;
+  int sym_split;   // blockIdx.y extent of uf_sym_kernel
 };
 
 // One place decides the decomposition; rmb_workspace_bytes and the launch
@@ -344,6 +495,16 @@ int make_plan(int block, int precision, long n_tgt, long n_src, const double* L,
   p.off_damp = align_up(p.rec_bytes, 256);
   p.off_partial = align_up(p.off_damp + (size_t)n_src * sizeof(double), 256);
   p.total = p.off_partial + (p.n_split > 1 ? (size_t)p.n_split * n_tgt * 3 * word : 0);
+  // accumulators of the pair-symmetric kernel (fp64 single-wall UF over all blobs)
+  p.off_acc = align_up(p.total, 256);
+  p.sym_split = 1;
+  if (block == RMB_UF && precision == RMB_FP64 && n_tgt == n_src) {
+    p.total = p.off_acc + (size_t)p.n_tiles * TILE * 3 * sizeof(double);
+    const int rows = p.n_tiles * (TILE / TPB);
+    int ss = (RMB_WAVES * sms * 4 + rows - 1) / (rows > 0 ? rows : 1);
+    if (ss > p.n_tiles / 4) ss = p.n_tiles / 4;
+    p.sym_split = ss < 1 ? 1 : ss;
+  }
   return 0;
 }
 
@@ -397,6 +558,33 @@ int launch(const Call& c)
     finish_kernel<T, BLOCK, WALL, PERIODIC><<<(unsigned)((c.n_tgt + 127) / 128), 128, 0, c.stream>>>(A);
   const cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail_cuda(e, "rmb_mobility_product launch");
+  return 0;
+}
+
+// Pair-symmetric path: single-wall UF, fp64, open boundaries, every blob a target.
+int launch_symmetric(const Call& c)
+{
+  const Plan& p = c.plan;
+  SrcRec<double, 1>* rec = reinterpret_cast<SrcRec<double, 1>*>(c.ws);
+  double* damp = reinterpret_cast<double*>(c.ws + p.off_damp);
+  double* acc = reinterpret_cast<double*>(c.ws + p.off_acc);
+  const long n_pad = (long)p.n_tiles * TILE;
+  const int in_plane = (c.flags & RMB_IN_PLANE) ? 1 : 0;
+  prepare_kernel<double, 1><<<(unsigned)((n_pad + 255) / 256), 256, 0, c.stream>>>(
+      c.n_src, n_pad, c.r, c.va, c.vb, c.a, 1, 1, in_plane, rec, damp);
+  cudaError_t e = cudaMemsetAsync(acc, 0, (size_t)n_pad * 3 * sizeof(double), c.stream);
+  if (e != cudaSuccess) return fail_cuda(e, "rmb_mobility_product (symmetric) memset");
+  SymArgs A;
+  A.src = rec; A.acc = acc; A.n_tiles = p.n_tiles; A.n_split = p.sym_split;
+  A.row_first = 0; A.row_stride = 1;
+  A.K = make_uf_ctx<double>(0.0);
+  const dim3 grid((unsigned)(n_pad / TPB), (unsigned)p.sym_split);
+  if (c.flags & RMB_NO_TMA) uf_sym_kernel<false><<<grid, TPB, 0, c.stream>>>(A);
+  else uf_sym_kernel<true><<<grid, TPB, 0, c.stream>>>(A);
+  sym_finish_kernel<<<(unsigned)((c.n_tgt + 127) / 128), 128, 0, c.stream>>>(rec, acc, damp, c.tgt_off, c.n_tgt,
+                                                                           block_norm(UF, c.eta, c.a), in_plane, c.out);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return fail_cuda(e, "rmb_mobility_product (symmetric) launch");
   return 0;
 }
 
@@ -493,6 +681,9 @@ int rmb_mobility_product(int block, int wall, int precision, int flags, long n_t
   if (rc != 0) return rc;
   if (workspace_bytes < c.plan.total) return fail(RMB_E_WORKSPACE, "workspace smaller than rmb_workspace_bytes()");
   const bool per = c.L[0] > 0 || c.L[1] > 0 || c.L[2] > 0;
+  if ((flags & RMB_SYMMETRIC) && block == RMB_UF && wall == RMB_SINGLE_WALL && precision == RMB_FP64 && !per &&
+      n_targets == n_sources && TILE % TPB == 0)
+    return launch_symmetric(c);
   return precision == RMB_FP32 ? launch_block<float>(c, per) : launch_block<double>(c, per);
 }
 

@@ -29,7 +29,8 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import FP32, FP64, FREE_SURFACE, IN_PLANE, NO_TMA, NO_WALL, SINGLE_WALL, UF, UF_UT, UT, WF, WT  # noqa: F401
+from ._lib import (FP32, FP64, FREE_SURFACE, IN_PLANE, NO_TMA, NO_WALL, SINGLE_WALL, SYMMETRIC, UF, UF_UT, UT, WF,  # noqa: F401
+                   WT)
 
 _workspaces = {}
 default_flags = int(os.environ.get("RMB_FLAGS", "0"))  # OR-ed into every call (debug: RMB_FLAGS=2 -> RMB_NO_TMA)

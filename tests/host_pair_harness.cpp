@@ -152,3 +152,35 @@ extern "C" void host_st(int wallmode, int fp32, long nt, long ns, const double* 
   if (fp32) { RMB_ST(float) } else { RMB_ST(double) }
 #undef RMB_ST
 }
+
+// ---- pair-symmetric evaluation (pair_uf_wall_sym): every unordered pair once, both directions ----
+extern "C" void host_uf_sym(long n, const double* r, const double* f, double eta, double a, double* out)
+{
+  typedef double T;
+  std::vector<SrcRec<T, 1>> rec(n);
+  std::vector<double> damp(n), u(3 * n, 0.0);
+  const double inva = 1.0 / a;
+  for (long j = 0; j < n; j++) {
+    double z = r[3 * j + 2];
+    const double B = (z < a) ? z / a : 1.0;
+    z = (z <= a) ? a : z;
+    damp[j] = B;
+    rec[j].x = r[3 * j] * inva; rec[j].y = r[3 * j + 1] * inva; rec[j].z = z * inva;
+    for (int c = 0; c < 3; c++) rec[j].v[c] = B * f[3 * j + c];
+  }
+  for (long i = 0; i < n; i++) {
+    const UfCtx<T> C = make_uf_ctx<T>(rec[i].z);
+    for (long j = i + 1; j < n; j++) {
+      const T rx = rec[i].x - rec[j].x, ry = rec[i].y - rec[j].y, rz = rec[i].z - rec[j].z;
+      const T r2 = rx * rx + ry * ry + rz * rz;
+      pair_uf_wall_sym<T, true>(rx, ry, rz, rec[i].z + rec[j].z, rec[i].z, rec[j].z, C, rec[i].v, rec[j].v, lt4(r2), r2,
+                                &u[3 * i], &u[3 * j]);
+    }
+  }
+  const double norm = block_norm(UF, eta, a);
+  for (long i = 0; i < n; i++) {
+    T ux = u[3 * i], uy = u[3 * i + 1], uz = u[3 * i + 2];
+    self_apply<T, UF, true>(rec[i].z, rec[i].v, ux, uy, uz);
+    out[3 * i] = ux * norm * damp[i]; out[3 * i + 1] = uy * norm * damp[i]; out[3 * i + 2] = uz * norm * damp[i];
+  }
+}

@@ -34,6 +34,14 @@ def harness(tmp_path_factory):
                     p(arrs[3]), p(arrs[4]), eta, p(arrs[5]), p(out))
         return out
 
+    lib.host_uf_sym.argtypes = [ctypes.c_long, dp, dp, ctypes.c_double, ctypes.c_double, dp]
+
+    def run_sym(r, f, eta, a):
+        r = np.ascontiguousarray(r, dtype=np.float64); f = np.ascontiguousarray(f, dtype=np.float64)
+        out = np.empty(r.size)
+        lib.host_uf_sym(r.shape[0], r.ctypes.data_as(dp), f.ctypes.data_as(dp), eta, a, out.ctypes.data_as(dp))
+        return out
+
     def run(block, wall, r, va, eta, a, L, fp32=False, in_plane=False, vb=None):
         r = np.ascontiguousarray(r, dtype=np.float64)
         va = np.ascontiguousarray(va, dtype=np.float64)
@@ -44,6 +52,7 @@ def harness(tmp_path_factory):
         lib.host_mf(BLOCKS[block], int(wall), int(fp32), r.shape[0], p(r), p(va), p(vb), eta, a, p(L), int(in_plane), p(out))
         return out
     run.st = run_st
+    run.sym = run_sym
     return run
 
 
@@ -116,3 +125,11 @@ def test_source_target_algebra(harness, case, fp32):
         assert relerr(out, g[case]) < 1e-3
     else:
         assert relerr(out, g[case]) < (1e-5 if fp32 else 1e-12)
+
+
+@pytest.mark.parametrize("cloud", ["dense", "dilute", "c1"])
+def test_pair_symmetric_evaluation(golden, harness, cloud):
+    """pair_uf_wall_sym: each unordered pair once, u_i += M_ij f_j and u_j += M_ji f_i from shared coefficients"""
+    r, v = golden[f"{cloud}/r"], golden[f"{cloud}/v"]
+    a, eta = golden[f"{cloud}/a_eta"]
+    assert relerr(harness.sym(r, v, eta, a), golden[f"{cloud}/open/single_wall/UF"]) < 1e-12
