@@ -22,7 +22,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 FLOP_PER_PAIR = 200.0   # algorithmic flop of one single-wall UF pair as the oracle writes it
-FP64_INSTR_PER_PAIR = 66  # FP64-pipe instructions the kernel executes per far pair (SASS count)
+FP64_INSTR_PER_PAIR = 43.5  # FP64-pipe instructions per interaction of the pair-symmetric kernel: 87 per unordered
+                            # far pair = two interactions (SASS count); the row kernel executes 66
 METRIC = "single-wall fp64 Mf pair-interactions/s at N=1M"
 
 
@@ -189,20 +190,16 @@ def run_b200(args):
     u_loc = torch.empty(3 * cnt, dtype=torch.float64, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
 
-    def gather_forces():
-        if world == 1:
-            return f_loc
-        if equal:
-            dist.all_gather_into_tensor(f_full, f_loc)
-        else:
-            parts = [f_full[3 * cuts[k]:3 * cuts[k + 1]] for k in range(world)]
-            dist.all_gather(parts, f_loc)
-        return f_full
+    # targets sharded by rank; the pair-symmetric schedule deals the unordered pairs to the ranks, every rank
+    # all-gathers the force slices, accumulates raw sums for all blobs, all-reduces them and finishes its shard
+    from rigidmultiblobswall_b200 import parallel
+    sm = parallel.ShardedMobility(r_d, eta, a, group=dist.group.WORLD if world > 1 else False,
+                                  ranges=[(cuts[k], cuts[k + 1] - cuts[k]) for k in range(world)])
+    assert sm.symmetric or n < 16384
 
     def step():
         flush.zero_()                       # L2 flush between iterations (inside the timed region; ~0.1 ms)
-        fv = gather_forces()
-        mb.mobility_product(mb.UF, mb.SINGLE_WALL, r_d, fv, eta, a, targets=(off, cnt), out=u_loc)
+        u_loc.copy_(sm(f_loc))
 
     def barrier():
         if world > 1:
@@ -248,9 +245,16 @@ def run_b200(args):
     r_host = torch.from_numpy(r_np).pin_memory().numpy()
     f_host = torch.from_numpy(f_np).pin_memory().numpy()
 
+    acc_e2e = [None]
+
     def e2e_step():
-        u = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r_host, f_host, eta, a, targets=(off, cnt))
-        return u
+        if world == 1:
+            return mb.mobility_product(mb.UF, mb.SINGLE_WALL, r_host, f_host, eta, a)     # NumPy in, NumPy out
+        r_t = torch.from_numpy(r_host).to(dev, non_blocking=True)
+        f_t = torch.from_numpy(f_host).to(dev, non_blocking=True)
+        acc_e2e[0] = mb.symmetric_partial(r_t, f_t, eta, a, rank=rank, world=world, acc=acc_e2e[0])
+        dist.all_reduce(acc_e2e[0])
+        return mb.symmetric_finish(n, acc_e2e[0], eta, a, targets=(off, cnt)).cpu().numpy()
 
     e2e_step()
     ms_e2e = timed(e2e_step, args.steps)
@@ -266,11 +270,11 @@ def run_b200(args):
         solve = gmres_mobility_solve()
 
     if rank == 0:
-        # dominant kernel = mf_kernel<double,UF,wall,open,TMA>; one launch per step per rank; the
-        # step's other launches (L2 flush memset, prepare_kernel) are < 0.1% of it
+        # dominant kernel = uf_sym_kernel<TMA>; one launch per step per rank; the step's other launches
+        # (L2 flush memset, prepare_kernel, accumulator memset, sym_finish_kernel) are < 0.1% of it
         launch_ms = ms / args.steps
-        achieved = (float(cnt) * n * FLOP_PER_PAIR) / (launch_ms * 1e-3) / 1e12
-        plan_launches = int(_lib.load().rmb_launches_per_product(mb.UF, mb.FP64, cnt, n, None))
+        achieved = (float(n) * n / world * FLOP_PER_PAIR) / (launch_ms * 1e-3) / 1e12   # this rank's share of the pairs
+        plan_launches = int(_lib.load().rmb_launches_per_product(mb.UF, mb.SINGLE_WALL, mb.FP64, 0, n, n, None))
         sms = _lib.load().rmb_device_sm_count()
         nominal = sms * 64 * 2 * (clocks.get("sm_mhz") or 1965.0) * 1e6 / 1e12   # 64 FP64 FMA lanes / clk / SM
         traffic = None
@@ -282,7 +286,9 @@ def run_b200(args):
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "C4: single-wall UF, N=%d random blobs, 10%% volume fraction, open boundaries" % n,
-                       "sharding": "targets by rank, sources replicated, NCCL all-gather of force slices per step"
+                       "kernel": "pair-symmetric (every unordered pair once, both blobs updated)",
+                       "sharding": "unordered pairs dealt to ranks by row group; per step NCCL all-gather of force "
+                                   "slices + all-reduce of the raw sums (24 N bytes); each rank finishes its targets"
                        if world > 1 else "single GPU",
                        "l2": "flushed between iterations (256 MiB memset inside the timed region)"},
             "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak_flops / 1e12, "unit": "TFLOP/s",

@@ -58,7 +58,11 @@ extern "C" {
 #define RMB_NO_TMA 2      /* stage source tiles with plain loads instead of cp.async.bulk (debug) */
 #define RMB_SYMMETRIC 4   /* single-wall RMB_UF, fp64, open boundaries, n_targets == n_sources: evaluate every
                              unordered pair once and update both blobs (sums accumulated with atomics: results
-                             agree with the default path to rounding, but are not bit-reproducible run to run) */
+                             agree with the row kernel to rounding, but are not bit-reproducible run to run).
+                             Without this flag the symmetric kernel is still chosen for eligible calls with
+                             n_sources >= RMB_SYMMETRIC_MIN_N */
+#define RMB_DETERMINISTIC 8 /* never use the pair-symmetric kernel: one thread per target, fixed summation order */
+#define RMB_SYMMETRIC_MIN_N 16384
 
 /* error codes */
 #define RMB_E_ARG (-1)        /* invalid argument                          */
@@ -78,8 +82,9 @@ int rmb_device_sm_count(void);
  */
 size_t rmb_workspace_bytes(int block, int precision, long n_targets, long n_sources, const double *L);
 
-/* Kernels one rmb_mobility_product() call launches for this problem (2, or 3 when sources are split). */
-int rmb_launches_per_product(int block, int precision, long n_targets, long n_sources, const double *L);
+/* Kernels one rmb_mobility_product() call launches for this problem (2 or 3). */
+int rmb_launches_per_product(int block, int wall, int precision, int flags, long n_targets, long n_sources,
+                             const double *L);
 
 /*
  * out[0:3*n_targets] = rows [target_offset, target_offset + n_targets) of
@@ -104,6 +109,24 @@ int rmb_mobility_product(int block, int wall, int precision, int flags,
                          const double *r_sources, const double *vec_a, const double *vec_b,
                          double eta, double a, const double *L,
                          double *out, void *workspace, size_t workspace_bytes, void *stream);
+
+/*
+ * Multi-rank form of the pair-symmetric single-wall UF product (fp64, open boundaries, all n blobs targets
+ * and sources).  Every rank calls
+ *   rmb_symmetric_partial()  raw pair sums, for ALL blobs, of this rank's share of the unordered pairs (row groups
+ *                            rank, rank + world, ... of the triangular schedule) -> acc, overwritten;
+ *                            acc: device, rmb_symmetric_acc_len(n) doubles
+ *   [sum acc over the ranks, e.g. ncclAllReduce]
+ *   rmb_symmetric_finish()   out = B (acc + self term) / (8 pi eta a) for targets [target_offset, +n_targets);
+ *                            same workspace as the partial call (it holds the packed records and the damping)
+ * rank = 0, world = 1 is what rmb_mobility_product(RMB_UF, RMB_SINGLE_WALL, RMB_FP64, RMB_SYMMETRIC, ...) does.
+ * workspace: >= rmb_workspace_bytes(RMB_UF, RMB_FP64, n, n, NULL).
+ */
+size_t rmb_symmetric_acc_len(long n);
+int rmb_symmetric_partial(int flags, long n, int rank, int world, const double *r, const double *force,
+                          double eta, double a, double *acc, void *workspace, size_t workspace_bytes, void *stream);
+int rmb_symmetric_finish(int flags, long n, long target_offset, long n_targets, const double *acc, double eta,
+                         double a, double *out, void *workspace, size_t workspace_bytes, void *stream);
 
 /*
  * Source-target UF product with per-blob radii: the flow at n_targets blobs

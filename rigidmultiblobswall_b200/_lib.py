@@ -10,7 +10,7 @@ from . import _build
 UF, UT, WF, WT, UF_UT = 0, 1, 2, 3, 4
 NO_WALL, SINGLE_WALL, FREE_SURFACE = 0, 1, 2
 FP64, FP32 = 0, 1
-IN_PLANE, NO_TMA, SYMMETRIC = 1, 2, 4
+IN_PLANE, NO_TMA, SYMMETRIC, DETERMINISTIC = 1, 2, 4, 8
 
 _lib = None
 
@@ -35,8 +35,8 @@ def load():
     lib.rmb_workspace_bytes.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_long, ctypes.c_long,
                                         ctypes.POINTER(ctypes.c_double)]
     lib.rmb_launches_per_product.restype = ctypes.c_int
-    lib.rmb_launches_per_product.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_long, ctypes.c_long,
-                                             ctypes.POINTER(ctypes.c_double)]
+    lib.rmb_launches_per_product.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_long,
+                                             ctypes.c_long, ctypes.POINTER(ctypes.c_double)]
     lib.rmb_mobility_product.restype = ctypes.c_int
     lib.rmb_mobility_product.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                          ctypes.c_long, ctypes.c_long, ctypes.c_long,
@@ -49,6 +49,14 @@ def load():
     lib.rmb_mobility_source_target.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_long, ctypes.c_long,
                                                c_dp, c_dp, c_dp, c_dp, c_dp, ctypes.c_double,
                                                ctypes.POINTER(ctypes.c_double), c_dp, c_dp, ctypes.c_size_t, c_dp]
+    lib.rmb_symmetric_acc_len.restype = ctypes.c_size_t
+    lib.rmb_symmetric_acc_len.argtypes = [ctypes.c_long]
+    lib.rmb_symmetric_partial.restype = ctypes.c_int
+    lib.rmb_symmetric_partial.argtypes = [ctypes.c_int, ctypes.c_long, ctypes.c_int, ctypes.c_int, c_dp, c_dp,
+                                          ctypes.c_double, ctypes.c_double, c_dp, c_dp, ctypes.c_size_t, c_dp]
+    lib.rmb_symmetric_finish.restype = ctypes.c_int
+    lib.rmb_symmetric_finish.argtypes = [ctypes.c_int, ctypes.c_long, ctypes.c_long, ctypes.c_long, c_dp,
+                                         ctypes.c_double, ctypes.c_double, c_dp, c_dp, ctypes.c_size_t, c_dp]
     lib.rmb_fma_peak.restype = ctypes.c_int
     lib.rmb_fma_peak.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double),
                                  ctypes.POINTER(ctypes.c_double)]

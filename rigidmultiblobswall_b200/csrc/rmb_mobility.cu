@@ -562,30 +562,52 @@ int launch(const Call& c)
 }
 
 // Pair-symmetric path: single-wall UF, fp64, open boundaries, every blob a target.
-int launch_symmetric(const Call& c)
+// Step 1: records + raw pair sums of the row groups row_first, row_first + row_stride, ... into acc.
+int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
 {
   const Plan& p = c.plan;
   SrcRec<double, 1>* rec = reinterpret_cast<SrcRec<double, 1>*>(c.ws);
   double* damp = reinterpret_cast<double*>(c.ws + p.off_damp);
-  double* acc = reinterpret_cast<double*>(c.ws + p.off_acc);
   const long n_pad = (long)p.n_tiles * TILE;
   const int in_plane = (c.flags & RMB_IN_PLANE) ? 1 : 0;
   prepare_kernel<double, 1><<<(unsigned)((n_pad + 255) / 256), 256, 0, c.stream>>>(
       c.n_src, n_pad, c.r, c.va, c.vb, c.a, 1, 1, in_plane, rec, damp);
   cudaError_t e = cudaMemsetAsync(acc, 0, (size_t)n_pad * 3 * sizeof(double), c.stream);
-  if (e != cudaSuccess) return fail_cuda(e, "rmb_mobility_product (symmetric) memset");
+  if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: memset");
   SymArgs A;
   A.src = rec; A.acc = acc; A.n_tiles = p.n_tiles; A.n_split = p.sym_split;
-  A.row_first = 0; A.row_stride = 1;
+  A.row_first = row_first; A.row_stride = row_stride;
   A.K = make_uf_ctx<double>(0.0);
-  const dim3 grid((unsigned)(n_pad / TPB), (unsigned)p.sym_split);
-  if (c.flags & RMB_NO_TMA) uf_sym_kernel<false><<<grid, TPB, 0, c.stream>>>(A);
-  else uf_sym_kernel<true><<<grid, TPB, 0, c.stream>>>(A);
-  sym_finish_kernel<<<(unsigned)((c.n_tgt + 127) / 128), 128, 0, c.stream>>>(rec, acc, damp, c.tgt_off, c.n_tgt,
-                                                                           block_norm(UF, c.eta, c.a), in_plane, c.out);
+  const long rows_all = n_pad / TPB;
+  const long rows = (rows_all - row_first + row_stride - 1) / row_stride;
+  if (rows > 0) {
+    const dim3 grid((unsigned)rows, (unsigned)p.sym_split);
+    if (c.flags & RMB_NO_TMA) uf_sym_kernel<false><<<grid, TPB, 0, c.stream>>>(A);
+    else uf_sym_kernel<true><<<grid, TPB, 0, c.stream>>>(A);
+  }
   e = cudaGetLastError();
-  if (e != cudaSuccess) return fail_cuda(e, "rmb_mobility_product (symmetric) launch");
+  if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: launch");
   return 0;
+}
+
+// Step 2: out = B (acc + self term) / (8 pi eta a) for a target range (records and damping from step 1's workspace).
+int sym_finish(const Call& c, const double* acc)
+{
+  const Plan& p = c.plan;
+  const SrcRec<double, 1>* rec = reinterpret_cast<const SrcRec<double, 1>*>(c.ws);
+  const double* damp = reinterpret_cast<const double*>(c.ws + p.off_damp);
+  sym_finish_kernel<<<(unsigned)((c.n_tgt + 127) / 128), 128, 0, c.stream>>>(
+      rec, acc, damp, c.tgt_off, c.n_tgt, block_norm(UF, c.eta, c.a), (c.flags & RMB_IN_PLANE) ? 1 : 0, c.out);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: finish");
+  return 0;
+}
+
+int launch_symmetric(const Call& c)
+{
+  double* acc = reinterpret_cast<double*>(c.ws + c.plan.off_acc);
+  const int rc = sym_partial(c, acc, 0, 1);
+  return rc != 0 ? rc : sym_finish(c, acc);
 }
 
 template <typename T, int BLOCK>
@@ -646,11 +668,17 @@ size_t rmb_workspace_bytes(int block, int precision, long n_targets, long n_sour
   return p.total;
 }
 
-int rmb_launches_per_product(int block, int precision, long n_targets, long n_sources, const double* L)
+int rmb_launches_per_product(int block, int wall, int precision, int flags, long n_targets, long n_sources,
+                             const double* L)
 {
   Plan p;
   if (block < 0 || block > RMB_UF_UT || n_targets <= 0 || n_sources <= 0) return 0;
   if (make_plan(block, precision, n_targets, n_sources, L, p) != 0) return 0;
+  const bool per = L && (L[0] > 0 || L[1] > 0 || L[2] > 0);
+  const bool sym_ok = block == RMB_UF && wall == RMB_SINGLE_WALL && precision == RMB_FP64 && !per &&
+                      n_targets == n_sources;
+  const bool sym_want = (flags & RMB_SYMMETRIC) || (!(flags & RMB_DETERMINISTIC) && n_sources >= RMB_SYMMETRIC_MIN_N);
+  if (sym_ok && sym_want) return 3;     // prepare_kernel + uf_sym_kernel + sym_finish_kernel (+ one memset)
   return 2 + (p.n_split > 1 ? 1 : 0);   // prepare_kernel + mf_kernel (+ finish_kernel when sources are split)
 }
 
@@ -681,10 +709,60 @@ int rmb_mobility_product(int block, int wall, int precision, int flags, long n_t
   if (rc != 0) return rc;
   if (workspace_bytes < c.plan.total) return fail(RMB_E_WORKSPACE, "workspace smaller than rmb_workspace_bytes()");
   const bool per = c.L[0] > 0 || c.L[1] > 0 || c.L[2] > 0;
-  if ((flags & RMB_SYMMETRIC) && block == RMB_UF && wall == RMB_SINGLE_WALL && precision == RMB_FP64 && !per &&
-      n_targets == n_sources && TILE % TPB == 0)
-    return launch_symmetric(c);
+  // pair-symmetric kernel: forced by RMB_SYMMETRIC, chosen by default from RMB_SYMMETRIC_MIN_N blobs on
+  // (below that the row kernel is as fast), never with RMB_DETERMINISTIC
+  const bool sym_ok = block == RMB_UF && wall == RMB_SINGLE_WALL && precision == RMB_FP64 && !per &&
+                      n_targets == n_sources && TILE % TPB == 0;
+  const bool sym_want = (flags & RMB_SYMMETRIC) || (!(flags & RMB_DETERMINISTIC) && n_sources >= RMB_SYMMETRIC_MIN_N);
+  if (sym_ok && sym_want) return launch_symmetric(c);
   return precision == RMB_FP32 ? launch_block<float>(c, per) : launch_block<double>(c, per);
+}
+
+size_t rmb_symmetric_acc_len(long n)
+{
+  return n <= 0 ? 0 : (size_t)((n + TILE - 1) / TILE) * TILE * 3;
+}
+
+static int sym_call(Call& c, int flags, long n, const double* r, const double* force, double eta, double a,
+                    void* workspace, size_t workspace_bytes, void* stream)
+{
+  if (n <= 0) return fail(RMB_E_ARG, "n must be positive");
+  if (!workspace) return fail(RMB_E_ARG, "null device pointer");
+  if (!(a > 0) || !(eta > 0)) return fail(RMB_E_ARG, "a and eta must be positive");
+  if ((reinterpret_cast<uintptr_t>(workspace) & 15) != 0) return fail(RMB_E_ARG, "workspace must be 16-byte aligned");
+  c.block = RMB_UF; c.wall = RMB_SINGLE_WALL; c.precision = RMB_FP64; c.flags = flags;
+  c.n_tgt = n; c.n_src = n; c.tgt_off = 0;
+  c.r = r; c.va = force; c.vb = nullptr; c.eta = eta; c.a = a;
+  for (int d = 0; d < 3; d++) c.L[d] = 0.0;
+  c.out = nullptr; c.ws = static_cast<char*>(workspace); c.stream = static_cast<cudaStream_t>(stream);
+  const int rc = make_plan(RMB_UF, RMB_FP64, n, n, c.L, c.plan);
+  if (rc != 0) return rc;
+  if (workspace_bytes < c.plan.total) return fail(RMB_E_WORKSPACE, "workspace smaller than rmb_workspace_bytes()");
+  return 0;
+}
+
+int rmb_symmetric_partial(int flags, long n, int rank, int world, const double* r, const double* force, double eta,
+                          double a, double* acc, void* workspace, size_t workspace_bytes, void* stream)
+{
+  if (world < 1 || rank < 0 || rank >= world) return fail(RMB_E_ARG, "0 <= rank < world required");
+  if (!r || !force || !acc) return fail(RMB_E_ARG, "null device pointer");
+  Call c;
+  const int rc = sym_call(c, flags, n, r, force, eta, a, workspace, workspace_bytes, stream);
+  return rc != 0 ? rc : sym_partial(c, acc, rank, world);
+}
+
+int rmb_symmetric_finish(int flags, long n, long target_offset, long n_targets, const double* acc, double eta,
+                         double a, double* out, void* workspace, size_t workspace_bytes, void* stream)
+{
+  if (target_offset < 0 || n_targets < 0 || target_offset + n_targets > n)
+    return fail(RMB_E_ARG, "target range must lie inside [0, n)");
+  if (n_targets == 0) return 0;
+  if (!acc || !out) return fail(RMB_E_ARG, "null device pointer");
+  Call c;
+  const int rc = sym_call(c, flags, n, nullptr, nullptr, eta, a, workspace, workspace_bytes, stream);
+  if (rc != 0) return rc;
+  c.tgt_off = target_offset; c.n_tgt = n_targets; c.out = out;
+  return sym_finish(c, acc);
 }
 
 int rmb_fma_peak(int precision, int iters, double* flops, double* elapsed_ms)

@@ -29,8 +29,8 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import (FP32, FP64, FREE_SURFACE, IN_PLANE, NO_TMA, NO_WALL, SINGLE_WALL, SYMMETRIC, UF, UF_UT, UT, WF,  # noqa: F401
-                   WT)
+from ._lib import (DETERMINISTIC, FP32, FP64, FREE_SURFACE, IN_PLANE, NO_TMA, NO_WALL, SINGLE_WALL, SYMMETRIC, UF,  # noqa: F401
+                   UF_UT, UT, WF, WT)
 
 _workspaces = {}
 default_flags = int(os.environ.get("RMB_FLAGS", "0"))  # OR-ed into every call (debug: RMB_FLAGS=2 -> RMB_NO_TMA)
@@ -135,6 +135,40 @@ def mobility_radii_trans_times_force(r_vectors, force, eta, a, radius_blobs, fun
     """mobility.py:1369: M f for blobs with different radii; `function` is one of the *_source_target_* products
     (the argument `a` is ignored, as in the reference)."""
     return function(r_vectors, r_vectors, force, radius_blobs, radius_blobs, eta, *args, **kwargs)
+
+
+def symmetric_partial(r_vectors, force, eta, a, rank=0, world=1, acc=None, flags=0):
+    """Multi-rank pair-symmetric single-wall UF product, step 1 (rmb_symmetric_partial): this rank's share of
+    the unordered pairs, raw sums for ALL blobs -> acc (device tensor, summed over the ranks by the caller)."""
+    lib = _lib.load()
+    dev = _device(r_vectors.device if isinstance(r_vectors, torch.Tensor) else None)
+    n = (r_vectors.numel() if isinstance(r_vectors, torch.Tensor) else np.asarray(r_vectors).size) // 3
+    with torch.cuda.device(dev):
+        r = _as_device_f64(r_vectors, 3 * n, dev)
+        f = _as_device_f64(force, 3 * n, dev)
+        if acc is None:
+            acc = torch.empty(lib.rmb_symmetric_acc_len(n), dtype=torch.float64, device=dev)
+        ws = _workspace(lib.rmb_workspace_bytes(UF, FP64, n, n, None), dev)
+        _lib.check(lib.rmb_symmetric_partial(flags | default_flags, n, rank, world, r.data_ptr(), f.data_ptr(),
+                                             float(eta), float(a), acc.data_ptr(), ws.data_ptr(), ws.numel(),
+                                             torch.cuda.current_stream(dev).cuda_stream))
+    return acc
+
+
+def symmetric_finish(n, acc, eta, a, targets=None, out=None, flags=0):
+    """Step 2 (rmb_symmetric_finish) after the ranks' acc have been summed: self term, normalisation, damping for
+    the target range.  Must follow symmetric_partial on the same device (it reads its workspace)."""
+    lib = _lib.load()
+    dev = acc.device
+    off, cnt = (0, n) if targets is None else targets
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty(3 * cnt, dtype=torch.float64, device=dev)
+        ws = _workspace(lib.rmb_workspace_bytes(UF, FP64, n, n, None), dev)
+        _lib.check(lib.rmb_symmetric_finish(flags | default_flags, n, off, cnt, acc.data_ptr(), float(eta), float(a),
+                                            out.data_ptr(), ws.data_ptr(), ws.numel(),
+                                            torch.cuda.current_stream(dev).cuda_stream))
+    return out
 
 
 def _make(block, wall, flags=0, precision=FP64, doc=""):

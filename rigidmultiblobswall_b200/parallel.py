@@ -70,7 +70,7 @@ class ShardedMobility:
     the blob part of linear_operator_rigid."""
 
     def __init__(self, r_vectors, eta, a, block=_mb.UF, wall=_mb.SINGLE_WALL, periodic_length=None,
-                 precision=_mb.FP64, group=None, ranges=None, boundaries=None, local_product=None):
+                 precision=_mb.FP64, group=None, ranges=None, boundaries=None, local_product=None, symmetric=None):
         single = group is False or not dist.is_initialized()      # group=False: single process on purpose
         self.group = None if single else (dist.group.WORLD if group is None else group)
         self.world = 1 if single else dist.get_world_size(group)
@@ -85,9 +85,26 @@ class ShardedMobility:
             self.block, self.wall, r, v, self.eta, self.a, periodic_length=self.L, precision=self.precision,
             targets=targets))
 
+        # Pair-symmetric schedule (single-wall UF, fp64, open boundaries): the unordered pairs are dealt to the
+        # ranks row group by row group, every rank accumulates raw sums for ALL blobs, the sums are all-reduced
+        # (the one extra data-path collective: 24 N bytes) and each rank finishes its own target range.
+        no_L = periodic_length is None or not bool((np.asarray(
+            periodic_length.cpu() if isinstance(periodic_length, torch.Tensor) else periodic_length) > 0).any())
+        self.symmetric = (symmetric is not False and local_product is None and block == _mb.UF and
+                          wall == _mb.SINGLE_WALL and precision == _mb.FP64 and no_L and
+                          (symmetric is True or n >= 16384))
+        self._acc = None
+
     def __call__(self, vec_local):
         full = self.vec.gather(vec_local)
-        return self._product(self.r, full, (self.offset, self.count))
+        if not self.symmetric:
+            return self._product(self.r, full, (self.offset, self.count))
+        n = self.r.numel() // 3
+        self._acc = _mb.symmetric_partial(self.r, full, self.eta, self.a, rank=self.rank, world=self.world,
+                                          acc=self._acc)
+        if self.world > 1:
+            dist.all_reduce(self._acc, group=self.group)
+        return _mb.symmetric_finish(n, self._acc, self.eta, self.a, targets=(self.offset, self.count))
 
 
 def _global_norm(x, group):

@@ -235,3 +235,43 @@ def test_symmetric_large_matches_default_and_in_plane(mb):
     # a request the symmetric kernel does not cover (target subset) silently takes the default path
     part = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, flags=mb.SYMMETRIC, targets=(100, 300))
     assert relerr(part, ref_full := mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a)[300:1200]) < 1e-13
+
+
+def test_default_selection_and_deterministic_flag(mb):
+    """n >= RMB_SYMMETRIC_MIN_N: the pair-symmetric kernel is the default; RMB_DETERMINISTIC keeps the row kernel,
+    whose target shards re-assemble bit-exactly; the multi-rank form (partial / finish with world = 3 on one
+    device, sums added by hand) gives the same product."""
+    from rigidmultiblobswall_b200 import _lib
+    lib = _lib.load()
+    rng = np.random.default_rng(21)
+    n, a, eta = 20000, 0.13, 7.0
+    assert lib.rmb_launches_per_product(mb.UF, mb.SINGLE_WALL, mb.FP64, 0, n, n, None) == 3
+    side = (n * 4 * np.pi / 3 / 0.1) ** (1 / 3) * a
+    r = torch.from_numpy(side * rng.random((n, 3))).cuda()
+    f = torch.from_numpy(rng.standard_normal((n, 3))).cuda()
+    det = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, flags=mb.DETERMINISTIC)
+    det2 = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, flags=mb.DETERMINISTIC)
+    assert torch.equal(det, det2)
+    parts = [mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, targets=(o, c))
+             for o, c in ((0, 7000), (7000, 6000), (13000, 7000))]
+    assert torch.equal(torch.cat(parts), det)
+    sym = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a)
+    assert float(torch.linalg.norm(sym - det) / torch.linalg.norm(det)) < 1e-13
+    world = 3
+    acc = sum(mb.symmetric_partial(r, f, eta, a, rank=k, world=world).clone() for k in range(world))
+    mb.symmetric_partial(r, f, eta, a, rank=0, world=world)       # finish reads the records of the last partial
+    out = torch.cat([mb.symmetric_finish(n, acc, eta, a, targets=t) for t in ((0, 9000), (9000, 11000))])
+    assert float(torch.linalg.norm(out - det) / torch.linalg.norm(det)) < 1e-13
+
+
+def test_sharded_mobility_single_rank_uses_symmetric_kernel(mb):
+    from rigidmultiblobswall_b200 import parallel
+    rng = np.random.default_rng(22)
+    n, a, eta = 17000, 0.2, 1.0
+    r = torch.from_numpy(9.0 * rng.random((n, 3))).cuda()
+    f = torch.from_numpy(rng.standard_normal((n, 3))).cuda().reshape(-1)
+    sm = parallel.ShardedMobility(r, eta, a, group=False)
+    assert sm.symmetric
+    ref = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, flags=mb.DETERMINISTIC)
+    assert float(torch.linalg.norm(sm(f) - ref) / torch.linalg.norm(ref)) < 1e-13
+    assert not parallel.ShardedMobility(r, eta, a, group=False, periodic_length=np.array([30.0, 0, 0])).symmetric
