@@ -190,7 +190,7 @@ RMB_HD void pair_uf(const PairGeom<T>& p, const UfCtx<T>& C, T fx, T fy, T fz, b
 //     B_f = b' (S + r_z f_z)              (free space, even in r)
 //     R.f = s S + R_z f_z,   G = p2 (R.f) + 2 p3h f_z,   SZh = p4h (R.f) - 2 p5q f_z
 //     u_xy += A_f f_xy + (B_f + s q^3 G) r_xy,   u_z += A_f f_z + B_f r_z + q^3 (G R_z + 2 SZh)
-// C holds the multiples of h_i (C.ht4 h_j = 4 h_i h_j, C.ht2 h_j = 2 h_i h_j).
+// hi2 = 2 h_i, hi4 = 4 h_i (per target, loop invariant); C: the literal constants.
 template <typename T, int SIGN>
 RMB_HD void uf_sym_direction(T rx, T ry, T rz, T Rz, T H, const T* f, T bp, T Af, T q3, T p2, T Zt, T vm, T ZtT, T tW,
                              T* u)
@@ -212,8 +212,8 @@ RMB_HD void uf_sym_direction(T rx, T ry, T rz, T Rz, T H, const T* f, T bp, T Af
 
 // (rx, ry, rz) = x_i - x_j, Rz = h_i + h_j (lengths / a); fi, fj: the two forces; BOTH: also update u_j.
 template <typename T, bool BOTH>
-RMB_HD void pair_uf_wall_sym(T rx, T ry, T rz, T Rz, T hi, T hj, const UfCtx<T>& C, const T* fi, const T* fj,
-                             bool any_near, T r2, T* ui, T* uj)
+RMB_HD void pair_uf_wall_sym(T rx, T ry, T rz, T Rz, T hi, T hj, T hi2, T hi4, const UfCtx<T>& C, const T* fi,
+                             const T* fj, bool any_near, T r2, T* ui, T* uj)
 {
   const T invr = rsqrt_full(r2);
   const T invr2 = invr * invr;
@@ -228,14 +228,14 @@ RMB_HD void pair_uf_wall_sym(T rx, T ry, T rz, T Rz, T hi, T hj, const UfCtx<T>&
     A = near ? An : A;
     bp = near ? bn : bp;
   }
-  const T q = rsqrt_full(RMB_FMA(C.ht4, hj, r2));
+  const T q = rsqrt_full(RMB_FMA(hi4, hj, r2));
   const T t = q * q;
   const T Aq = RMB_FMA(Rz, Rz, C.c13);
   const T Zt = Rz * t;
   const T t2 = t + t;
   const T k = Rz * Zt;
   const T q3 = q * t;
-  const T b2 = RMB_FMA(C.ht2, hj, C.c23);
+  const T b2 = RMB_FMA(hi2, hj, C.c23);
   const T X = RMB_FMA(C.cm53, k, Aq);
   const T Y = RMB_FMA(C.cm73, k, Aq);
   const T p1 = RMB_FMA(RMB_FMA(t2, X, -b2), t, T(-1.0));

@@ -40,6 +40,16 @@ namespace {
 #ifndef RMB_MINB
 #define RMB_MINB 1
 #endif
+#ifndef RMB_SYM_UNROLL
+#define RMB_SYM_UNROLL 1  // rotation-loop unroll of the pair-symmetric kernel
+#endif
+#ifndef RMB_SYM_NT
+#define RMB_SYM_NT 1      // blobs per lane of the pair-symmetric kernel (1 or 2; TILE must be a multiple of 128 NT).
+                          // Measured at N = 400k: 334.6 (1) vs 336.8 (2) G pairs/s, and 270 vs 252 at N = 20k
+#endif
+#ifndef RMB_SYM_MINB
+#define RMB_SYM_MINB 1
+#endif
 #ifndef RMB_WAVES
 #define RMB_WAVES 10
 #endif
@@ -309,7 +319,8 @@ __global__ void finish_kernel(const MfArgs<T, (BLOCK == UF_UT) ? 2 : 1> A)
 // M_ij f_j to its own u_i and M_ji f_i to a travelling accumulator that moves
 // one lane per step (3 x SHFL.64), so after 32 steps lane l holds the sum for
 // blob 32 J + l and flushes it with a global RED.  J == I is the diagonal block:
-// steps 1..31, one direction only.  A CTA = 4 warps = a row group of 128 blobs
+// steps 1..31, one direction only.  (Timing experiments: dropping the flush changes
+// nothing, dropping the shuffles gains 3.5 %.)  A CTA = 4 warps = a row group of 128 blobs
 // (blockIdx.x, scaled by the rank stride) x a range of source tiles
 // (blockIdx.y); rows are triangular (tiles >= the row's own), long rows first.
 // Sums are accumulated with atomics in acc[n_pad][3]; sym_finish_kernel adds the
@@ -322,31 +333,91 @@ struct SymArgs {
   UfCtx<double> K;
 };
 
-template <bool TMA>
-__global__ void __launch_bounds__(TPB, 1) uf_sym_kernel(const __grid_constant__ SymArgs A)
+// Registers of one lane: NT blobs, one from each of the warp's NT consecutive blocks.
+template <int NT>
+struct SymLane {
+  double x[NT], y[NT], h[NT], h2[NT], h4[NT], f[NT][3], u[NT][3];
+};
+
+// One block J against the lane's blobs k in [K0, K0 + NK): 32 rotation steps, both directions, then the
+// travelling accumulators (home again) are flushed to acc.
+template <int NT, int K0, int NK>
+__device__ __forceinline__ void sym_block(const double* __restrict__ blk, int lane, SymLane<NT>& L, const UfCtx<double>& C,
+                                          double* __restrict__ acc_j)
+{
+  typedef double T;
+  constexpr int W = 6;
+  T aj[3] = {0, 0, 0};
+  int jl = lane;
+  const int from = (lane + 1) & 31;
+  constexpr int SU = RMB_SYM_UNROLL;
+#pragma unroll SU
+  for (int s = 0; s < 32; s++) {
+    T w[W];
+    load_rec<W>(blk + jl * W, w);
+#pragma unroll
+    for (int k = K0; k < K0 + NK; k++) {
+      const T rx = L.x[k] - w[0], ry = L.y[k] - w[1], rz = L.h[k] - w[2];
+      const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
+      const bool any_near = __any_sync(0xffffffffu, lt4(r2));
+      pair_uf_wall_sym<T, true>(rx, ry, rz, L.h[k] + w[2], L.h[k], w[2], L.h2[k], L.h4[k], C, L.f[k], w + 3, any_near,
+                                r2, L.u[k], aj);
+    }
+    // the accumulator of blob j moves to the lane that meets j next
+    aj[0] = __shfl_sync(0xffffffffu, aj[0], from);
+    aj[1] = __shfl_sync(0xffffffffu, aj[1], from);
+    aj[2] = __shfl_sync(0xffffffffu, aj[2], from);
+    jl = (jl + 1) & 31;
+  }
+  atomicAdd(acc_j + 3 * lane, aj[0]); atomicAdd(acc_j + 3 * lane + 1, aj[1]); atomicAdd(acc_j + 3 * lane + 2, aj[2]);
+}
+
+// Diagonal block (J == the block of blob k): ordered pairs (l, (l + s) & 31), s = 1..31, one direction.
+template <int NT>
+__device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lane, SymLane<NT>& L, int k,
+                                         const UfCtx<double>& C)
+{
+  typedef double T;
+  constexpr int W = 6;
+#pragma unroll 2
+  for (int s = 1; s < 32; s++) {
+    T w[W];
+    load_rec<W>(blk + ((lane + s) & 31) * W, w);
+    const T rx = L.x[k] - w[0], ry = L.y[k] - w[1], rz = L.h[k] - w[2];
+    const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
+    const bool any_near = __any_sync(0xffffffffu, lt4(r2));
+    pair_uf_wall_sym<T, false>(rx, ry, rz, L.h[k] + w[2], L.h[k], w[2], L.h2[k], L.h4[k], C, L.f[k], w + 3, any_near, r2,
+                               L.u[k], L.u[k]);
+  }
+}
+
+template <bool TMA, int NT>
+__global__ void __launch_bounds__(TPB, RMB_SYM_MINB) uf_sym_kernel(const __grid_constant__ SymArgs A)
 {
   typedef double T;
   constexpr int W = 6;
   constexpr uint32_t TILE_BYTES = TILE * W * sizeof(T);
+  constexpr int ROW = TPB * NT;                            // blobs of one row group (CTA)
   __shared__ alignas(128) T tile[TMA ? STAGES : 1][TILE * W];
   __shared__ alignas(8) uint64_t full[STAGES];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int g = A.row_first + blockIdx.x * A.row_stride;   // row group of 128 blobs
-  const long I = (long)g * (TPB / 32) + warp;              // this warp's block of 32
-  const long gi = I * 32 + lane;
+  const int g = A.row_first + blockIdx.x * A.row_stride;   // row group of ROW blobs
+  const long I0 = ((long)g * (TPB / 32) + warp) * NT;      // this warp's first block of 32
 
-  T xi, yi, hi, fi[3];
-  {
-    const SrcRec<T, 1>& me = A.src[gi];
-    xi = me.x; yi = me.y; hi = me.z;
-    fi[0] = me.v[0]; fi[1] = me.v[1]; fi[2] = me.v[2];
+  SymLane<NT> L;
+#pragma unroll
+  for (int k = 0; k < NT; k++) {
+    const SrcRec<T, 1>& me = A.src[(I0 + k) * 32 + lane];
+    L.x[k] = me.x; L.y[k] = me.y; L.h[k] = me.z;
+    L.h2[k] = 2.0 * me.z; L.h4[k] = 4.0 * me.z;
+#pragma unroll
+    for (int c = 0; c < 3; c++) { L.f[k][c] = me.v[c]; L.u[k][c] = 0.0; }
   }
-  UfCtx<T> C = A.K;
-  set_target_height(C, hi);
+  const UfCtx<T>& C = A.K;
 
-  // this CTA's part of the row's tiles [g * TPB / TILE, n_tiles)
-  const int t_first = (int)(((long)g * TPB) / TILE);
+  // this CTA's part of the row's tiles [g * ROW / TILE, n_tiles)
+  const int t_first = (int)(((long)g * ROW) / TILE);
   const int len = A.n_tiles - t_first;
   const int v0 = t_first + (int)(((long)len * blockIdx.y) / A.n_split);
   const int v1 = t_first + (int)(((long)len * (blockIdx.y + 1)) / A.n_split);
@@ -365,7 +436,6 @@ __global__ void __launch_bounds__(TPB, 1) uf_sym_kernel(const __grid_constant__ 
     }
   }
 
-  T ui[3] = {0, 0, 0};
   int stage = 0;
   uint32_t phases = 0;
   for (int v = v0; v < v1; v++) {
@@ -383,47 +453,27 @@ __global__ void __launch_bounds__(TPB, 1) uf_sym_kernel(const __grid_constant__ 
     }
     const T* tp = tile[TMA ? stage : 0];
     for (int jb = 0; jb < TILE / 32; jb++) {
-      const long J = (long)v * (TILE / 32) + jb;
-      if (J < I) continue;                         // warp-uniform: that pair of blocks belongs to the other warp
+      const long J = (long)v * (TILE / 32) + jb;           // warp-uniform case split on J against I0 .. I0 + NT - 1
+      if (J < I0) continue;                                // those pairs of blocks belong to another warp
       const T* blk = tp + jb * 32 * W;
-      if (J == I) {
-        // diagonal block: ordered pairs (l, (l + s) & 31), s = 1..31, one direction
-#pragma unroll 2
-        for (int s = 1; s < 32; s++) {
-          T w[W];
-          load_rec<W>(blk + ((lane + s) & 31) * W, w);
-          const T rx = xi - w[0], ry = yi - w[1], rz = hi - w[2];
-          const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
-          const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-          pair_uf_wall_sym<T, false>(rx, ry, rz, hi + w[2], hi, w[2], C, fi, w + 3, any_near, r2, ui, ui);
-        }
-      } else {
-        T aj[3] = {0, 0, 0};
-        int jl = lane;
-#pragma unroll 2
-        for (int s = 0; s < 32; s++) {
-          T w[W];
-          load_rec<W>(blk + jl * W, w);
-          const T rx = xi - w[0], ry = yi - w[1], rz = hi - w[2];
-          const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
-          const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-          pair_uf_wall_sym<T, true>(rx, ry, rz, hi + w[2], hi, w[2], C, fi, w + 3, any_near, r2, ui, aj);
-          // the accumulator of blob j moves to the lane that meets j next
-          const int from = (lane + 1) & 31;
-          aj[0] = __shfl_sync(0xffffffffu, aj[0], from);
-          aj[1] = __shfl_sync(0xffffffffu, aj[1], from);
-          aj[2] = __shfl_sync(0xffffffffu, aj[2], from);
-          jl = (jl + 1) & 31;
-        }
-        double* a = A.acc + (size_t)(J * 32 + lane) * 3;   // after 32 moves lane l holds blob 32 J + l
-        atomicAdd(a, aj[0]); atomicAdd(a + 1, aj[1]); atomicAdd(a + 2, aj[2]);
+      double* acc_j = A.acc + (size_t)J * 32 * 3;
+      if (J >= I0 + NT) {
+        sym_block<NT, 0, NT>(blk, lane, L, C, acc_j);      // the hot path: all NT blobs of the lane meet block J
+      } else if (NT == 1 || J == I0) {
+        sym_diag<NT>(blk, lane, L, 0, C);
+      } else {                                             // NT == 2, J == I0 + 1
+        sym_block<NT, 0, 1>(blk, lane, L, C, acc_j);
+        sym_diag<NT>(blk, lane, L, NT - 1, C);
       }
     }
     __syncthreads();
     if (TMA) stage ^= 1;
   }
-  double* a = A.acc + (size_t)gi * 3;
-  atomicAdd(a, ui[0]); atomicAdd(a + 1, ui[1]); atomicAdd(a + 2, ui[2]);
+#pragma unroll
+  for (int k = 0; k < NT; k++) {
+    double* a = A.acc + (size_t)((I0 + k) * 32 + lane) * 3;
+    atomicAdd(a, L.u[k][0]); atomicAdd(a + 1, L.u[k][1]); atomicAdd(a + 2, L.u[k][2]);
+  }
 }
 
 // out = B (acc + self term) / (8 pi eta a) for the targets [tgt_off, tgt_off + n_tgt)
@@ -500,8 +550,8 @@ int make_plan(int block, int precision, long n_tgt, long n_src, const double* L,
   p.sym_split = 1;
   if (block == RMB_UF && precision == RMB_FP64 && n_tgt == n_src) {
     p.total = p.off_acc + (size_t)p.n_tiles * TILE * 3 * sizeof(double);
-    const int rows = p.n_tiles * (TILE / TPB);
-    int ss = (RMB_WAVES * sms * 4 + rows - 1) / (rows > 0 ? rows : 1);
+    const int rows = p.n_tiles * (TILE / (TPB * RMB_SYM_NT));
+    int ss = (RMB_WAVES * sms * 3 + rows - 1) / (rows > 0 ? rows : 1);
     if (ss > p.n_tiles / 4) ss = p.n_tiles / 4;
     p.sym_split = ss < 1 ? 1 : ss;
   }
@@ -578,12 +628,12 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
   A.src = rec; A.acc = acc; A.n_tiles = p.n_tiles; A.n_split = p.sym_split;
   A.row_first = row_first; A.row_stride = row_stride;
   A.K = make_uf_ctx<double>(0.0);
-  const long rows_all = n_pad / TPB;
+  const long rows_all = n_pad / (TPB * RMB_SYM_NT);
   const long rows = (rows_all - row_first + row_stride - 1) / row_stride;
   if (rows > 0) {
     const dim3 grid((unsigned)rows, (unsigned)p.sym_split);
-    if (c.flags & RMB_NO_TMA) uf_sym_kernel<false><<<grid, TPB, 0, c.stream>>>(A);
-    else uf_sym_kernel<true><<<grid, TPB, 0, c.stream>>>(A);
+    if (c.flags & RMB_NO_TMA) uf_sym_kernel<false, RMB_SYM_NT><<<grid, TPB, 0, c.stream>>>(A);
+    else uf_sym_kernel<true, RMB_SYM_NT><<<grid, TPB, 0, c.stream>>>(A);
   }
   e = cudaGetLastError();
   if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: launch");
@@ -712,7 +762,7 @@ int rmb_mobility_product(int block, int wall, int precision, int flags, long n_t
   // pair-symmetric kernel: forced by RMB_SYMMETRIC, chosen by default from RMB_SYMMETRIC_MIN_N blobs on
   // (below that the row kernel is as fast), never with RMB_DETERMINISTIC
   const bool sym_ok = block == RMB_UF && wall == RMB_SINGLE_WALL && precision == RMB_FP64 && !per &&
-                      n_targets == n_sources && TILE % TPB == 0;
+                      n_targets == n_sources && TILE % (TPB * RMB_SYM_NT) == 0;
   const bool sym_want = (flags & RMB_SYMMETRIC) || (!(flags & RMB_DETERMINISTIC) && n_sources >= RMB_SYMMETRIC_MIN_N);
   if (sym_ok && sym_want) return launch_symmetric(c);
   return precision == RMB_FP32 ? launch_block<float>(c, per) : launch_block<double>(c, per);

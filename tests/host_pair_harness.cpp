@@ -173,7 +173,8 @@ extern "C" void host_uf_sym(long n, const double* r, const double* f, double eta
     for (long j = i + 1; j < n; j++) {
       const T rx = rec[i].x - rec[j].x, ry = rec[i].y - rec[j].y, rz = rec[i].z - rec[j].z;
       const T r2 = rx * rx + ry * ry + rz * rz;
-      pair_uf_wall_sym<T, true>(rx, ry, rz, rec[i].z + rec[j].z, rec[i].z, rec[j].z, C, rec[i].v, rec[j].v, lt4(r2), r2,
+      pair_uf_wall_sym<T, true>(rx, ry, rz, rec[i].z + rec[j].z, rec[i].z, rec[j].z, C.ht2, C.ht4, C, rec[i].v, rec[j].v,
+                                lt4(r2), r2,
                                 &u[3 * i], &u[3 * j]);
     }
   }
