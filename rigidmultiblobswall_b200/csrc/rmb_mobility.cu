@@ -631,7 +631,13 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
   const long rows_all = n_pad / (TPB * RMB_SYM_NT);
   const long rows = (rows_all - row_first + row_stride - 1) / row_stride;
   if (rows > 0) {
-    const dim3 grid((unsigned)rows, (unsigned)p.sym_split);
+    // rows are triangular (1 .. n_tiles tiles): split them over blockIdx.y until THIS launch (a rank's share of
+    // the rows) has at least RMB_WAVES waves of resident CTAs, so that the tail is short
+    int split = (int)((RMB_WAVES * (long)sm_count() * 4 + rows - 1) / rows);
+    if (split > p.n_tiles / 4) split = p.n_tiles / 4;
+    if (split < 1) split = 1;
+    A.n_split = split;
+    const dim3 grid((unsigned)rows, (unsigned)split);
     if (c.flags & RMB_NO_TMA) uf_sym_kernel<false, RMB_SYM_NT><<<grid, TPB, 0, c.stream>>>(A);
     else uf_sym_kernel<true, RMB_SYM_NT><<<grid, TPB, 0, c.stream>>>(A);
   }
