@@ -57,6 +57,17 @@ RMB_HD double rsqrt_full(double x)
   return RMB_FMA(y0, p * e, y0);
 }
 RMB_HD float rsqrt_full(float x) { return rsqrt_fast(x); }
+// Same with the two literals of the correction handed in (from the kernel's constant bank: nvcc otherwise
+// re-materialises 0.375 with two moves in every loop iteration).
+RMB_HD double rsqrt_full(double x, double c38, double chalf)
+{
+  const double y0 = rsqrt_seed(x);
+  const double t = x * y0;
+  const double e = RMB_FMA(-t, y0, 1.0);
+  const double p = RMB_FMA(c38, e, chalf);
+  return RMB_FMA(y0, p * e, y0);
+}
+RMB_HD float rsqrt_full(float x, float, float) { return rsqrt_fast(x); }
 
 // "is r2 < 4" without touching the FP64 pipe: compare the high word.
 #if defined(RMB_HOST_ONLY)
@@ -106,7 +117,7 @@ struct PairGeom {
 template <typename T>
 struct UfCtx {
   T c13, c23, cm53, cm73, c103, c43;   // 1/3, 2/3, -5/3, -7/3, 10/3, 4/3
-  T k1, k2, k12, km20, km10, km3, khalf;   // 1, 2, 12, -20, -10, -3, 1/2 (second literal of two-literal FMAs)
+  T k1, k2, k12, km20, km10, km3, khalf, c38;   // 1, 2, 12, -20, -10, -3, 1/2, 3/8 (second literals of two-literal FMAs)
   T ht, ht2, ht4, ht6;                 // target height h_i and its multiples (wall form)
 };
 
@@ -117,7 +128,7 @@ RMB_HOST_DEVICE UfCtx<T> make_uf_ctx(T ht)
   C.c13 = T(1.0 / 3.0); C.c23 = T(2.0 / 3.0); C.cm53 = T(-5.0 / 3.0); C.cm73 = T(-7.0 / 3.0);
   C.c103 = T(10.0 / 3.0); C.c43 = T(4.0 / 3.0);
   C.k1 = T(1.0); C.k2 = T(2.0); C.k12 = T(12.0); C.km20 = T(-20.0); C.km10 = T(-10.0); C.km3 = T(-3.0);
-  C.khalf = T(0.5);
+  C.khalf = T(0.5); C.c38 = T(0.375);
   C.ht = ht; C.ht2 = T(2.0) * ht; C.ht4 = T(4.0) * ht; C.ht6 = T(6.0) * ht;
   return C;
 }
@@ -132,7 +143,7 @@ RMB_HD void pair_uf(const PairGeom<T>& p, const UfCtx<T>& C, T fx, T fy, T fz, b
                     T& uy, T& uz)
 {
   const T s = RMB_FMA(p.ry, fy, p.rx * fx);
-  const T invr = rsqrt_full(r2);
+  const T invr = rsqrt_full(r2, C.c38, C.khalf);
   const T invr2 = invr * invr;
   const T rf = RMB_FMA(p.rz, fz, s);
   const T invr3 = invr2 * invr;
@@ -152,7 +163,7 @@ RMB_HD void pair_uf(const PairGeom<T>& p, const UfCtx<T>& C, T fx, T fy, T fz, b
     ux = RMB_FMA(B, p.rx, ux); uy = RMB_FMA(B, p.ry, uy); uz = RMB_FMA(B, p.rz, uz);
   } else {
     // |R|^2 = rx^2 + ry^2 + Rz^2.  Without a z wrap rz = z_i - z_j, so |R|^2 = r^2 + 4 h_i h_j (one FMA, no Rz^2).
-    const T q = rsqrt_full(ZOPEN ? RMB_FMA(C.ht4, p.h, r2) : RMB_FMA(p.Rz, p.Rz, rxy2));
+    const T q = rsqrt_full(ZOPEN ? RMB_FMA(C.ht4, p.h, r2) : RMB_FMA(p.Rz, p.Rz, rxy2), C.c38, C.khalf);
     const T t = q * q;
     const T Aq = RMB_FMA(p.Rz, p.Rz, C.c13);             // alpha + 1/3
     const T Zt = p.Rz * t;
@@ -215,7 +226,7 @@ template <typename T, bool BOTH>
 RMB_HD void pair_uf_wall_sym(T rx, T ry, T rz, T Rz, T hi, T hj, T hi2, T hi4, const UfCtx<T>& C, const T* fi,
                              const T* fj, bool any_near, T r2, T* ui, T* uj)
 {
-  const T invr = rsqrt_full(r2);
+  const T invr = rsqrt_full(r2, C.c38, C.khalf);
   const T invr2 = invr * invr;
   const T invr3 = invr2 * invr;
   T A = RMB_FMA(C.c23, invr3, invr);
@@ -228,7 +239,7 @@ RMB_HD void pair_uf_wall_sym(T rx, T ry, T rz, T Rz, T hi, T hj, T hi2, T hi4, c
     A = near ? An : A;
     bp = near ? bn : bp;
   }
-  const T q = rsqrt_full(RMB_FMA(hi4, hj, r2));
+  const T q = rsqrt_full(RMB_FMA(hi4, hj, r2), C.c38, C.khalf);
   const T t = q * q;
   const T Aq = RMB_FMA(Rz, Rz, C.c13);
   const T Zt = Rz * t;
@@ -286,9 +297,9 @@ RMB_HD void self_uf(T h, T fx, T fy, T fz, T& ux, T& uy, T& uz)
 //       u_z = cz (q^3 c12' - kf),  P1 = kf r_z + q^3 c14,  E = t (10 Zt - 6h) cz,  cz = r_x t_y - r_y t_x
 // 50 (WF) / 47 (UT) FP64 instructions per far pair, was 70 / 68 in e-vector form.
 template <typename T>
-RMB_HD T coupling_k(T r2, bool any_near)
+RMB_HD T coupling_k(T r2, bool any_near, const UfCtx<T>& C)
 {
-  const T invr = rsqrt_full(r2);
+  const T invr = rsqrt_full(r2, C.c38, C.khalf);
   T k = invr * invr * invr;
   if (any_near) {
     const T kn = RMB_FMA(T(-0.1875), r2 * invr, T(0.5));
@@ -302,13 +313,13 @@ template <typename T, bool WALL, bool ZOPEN = false>
 RMB_HD void pair_wf(const PairGeom<T>& p, const UfCtx<T>& C, T fx, T fy, T fz, bool any_near, T r2, T rxy2, T& ux,
                     T& uy, T& uz)
 {
-  const T kf = coupling_k(r2, any_near);
+  const T kf = coupling_k(r2, any_near, C);
   if (!WALL) {
     ux = RMB_FMA(kf, RMB_FMA(p.rz, fy, -(p.ry * fz)), ux);
     uy = RMB_FMA(kf, RMB_FMA(p.rx, fz, -(p.rz * fx)), uy);
     uz = RMB_FMA(kf, RMB_FMA(p.ry, fx, -(p.rx * fy)), uz);
   } else {
-    const T q = rsqrt_full(ZOPEN ? RMB_FMA(C.ht4, p.h, r2) : RMB_FMA(p.Rz, p.Rz, rxy2));
+    const T q = rsqrt_full(ZOPEN ? RMB_FMA(C.ht4, p.h, r2) : RMB_FMA(p.Rz, p.Rz, rxy2), C.c38, C.khalf);
     const T t = q * q;
     const T Zt = p.Rz * t;
     const T q3 = q * t;
@@ -334,13 +345,13 @@ template <typename T, bool WALL, bool ZOPEN = false>
 RMB_HD void pair_ut(const PairGeom<T>& p, const UfCtx<T>& C, T tx, T ty, T tz, bool any_near, T r2, T rxy2, T& ux,
                     T& uy, T& uz)
 {
-  const T kf = coupling_k(r2, any_near);
+  const T kf = coupling_k(r2, any_near, C);
   if (!WALL) {
     ux = RMB_FMA(kf, RMB_FMA(p.rz, ty, -(p.ry * tz)), ux);
     uy = RMB_FMA(kf, RMB_FMA(p.rx, tz, -(p.rz * tx)), uy);
     uz = RMB_FMA(kf, RMB_FMA(p.ry, tx, -(p.rx * ty)), uz);
   } else {
-    const T q = rsqrt_full(ZOPEN ? RMB_FMA(C.ht4, p.h, r2) : RMB_FMA(p.Rz, p.Rz, rxy2));
+    const T q = rsqrt_full(ZOPEN ? RMB_FMA(C.ht4, p.h, r2) : RMB_FMA(p.Rz, p.Rz, rxy2), C.c38, C.khalf);
     const T t = q * q;
     const T Zt = p.Rz * t;
     const T q3 = q * t;
@@ -384,7 +395,7 @@ template <typename T, bool WALL, bool ZOPEN = false>
 RMB_HD void pair_wt(const PairGeom<T>& p, const UfCtx<T>& C, T tx, T ty, T tz, bool any_near, T r2, T rxy2, T& ux,
                     T& uy, T& uz)
 {
-  const T invr = rsqrt_full(r2);
+  const T invr = rsqrt_full(r2, C.c38, C.khalf);
   const T invr2 = invr * invr;
   const T invr3 = invr2 * invr;
   const T s = RMB_FMA(p.ry, ty, p.rx * tx);
@@ -406,7 +417,7 @@ RMB_HD void pair_wt(const PairGeom<T>& p, const UfCtx<T>& C, T tx, T ty, T tz, b
     // unnormalised wall term (cz = r_x t_y - r_y t_x, Rt = R.t, q5 = q^5):
     //   u_x += q^3 (1/2 - 3k) t_x - 3/2 q5 Rt r_x - 3 q5 cz r_y      u_y likewise with (+3 q5 cz r_x)
     //   u_z += q^3 (1/2 - 3k) t_z + 3/2 q5 Rt Rz
-    const T q = rsqrt_full(ZOPEN ? RMB_FMA(C.ht4, p.h, r2) : RMB_FMA(p.Rz, p.Rz, rxy2));
+    const T q = rsqrt_full(ZOPEN ? RMB_FMA(C.ht4, p.h, r2) : RMB_FMA(p.Rz, p.Rz, rxy2), C.c38, C.khalf);
     const T t = q * q;
     const T q3 = q * t;
     const T k = (p.Rz * p.Rz) * t;
