@@ -8,7 +8,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 SO = os.path.join(PKG, "librmb_mobility.so")
 SOURCES = ["rmb_mobility.cu", "rmb_source_target.cu", "rmb_rigid.cu"]
-HEADERS = ["pair_math.cuh", "mf_core.cuh", "tile_pipe.cuh", "st_math.cuh", os.path.join("..", "..", "include", "rmb_mobility.h"),
+HEADERS = ["pair_math.cuh", "mf_core.cuh", "tile_pipe.cuh", "st_math.cuh", "sym_schedule.cuh", os.path.join("..", "..", "include", "rmb_mobility.h"),
            os.path.join("..", "..", "include", "rmb_rigid.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC"]

@@ -18,6 +18,7 @@
 
 #include "../../include/rmb_mobility.h"
 #include "mf_core.cuh"
+#include "sym_schedule.cuh"
 #include "tile_pipe.cuh"
 
 using namespace rmb;
@@ -417,10 +418,8 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) uf_sym_kernel(const __grid_
   const UfCtx<T>& C = A.K;
 
   // this CTA's part of the row's tiles [g * ROW / TILE, n_tiles)
-  const int t_first = (int)(((long)g * ROW) / TILE);
-  const int len = A.n_tiles - t_first;
-  const int v0 = t_first + (int)(((long)len * blockIdx.y) / A.n_split);
-  const int v1 = t_first + (int)(((long)len * (blockIdx.y + 1)) / A.n_split);
+  const SymRowPart part = sym_row_part(g, ROW, TILE, A.n_tiles, (int)blockIdx.y, A.n_split);
+  const int v0 = part.v0, v1 = part.v1;
   const T* srcw = reinterpret_cast<const T*>(A.src);
 
   if (TMA) {
@@ -454,13 +453,13 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) uf_sym_kernel(const __grid_
     const T* tp = tile[TMA ? stage : 0];
     for (int jb = 0; jb < TILE / 32; jb++) {
       const long J = (long)v * (TILE / 32) + jb;           // warp-uniform case split on J against I0 .. I0 + NT - 1
-      if (J < I0) continue;                                // those pairs of blocks belong to another warp
+      if (sym_block_case(I0, J) == 0) continue;            // J < I0: those pairs of blocks belong to another warp
       const T* blk = tp + jb * 32 * W;
       double* acc_j = A.acc + (size_t)J * 32 * 3;
-      if (J >= I0 + NT) {
+      if (sym_block_case(I0 + NT - 1, J) == 2) {
         sym_block<NT, 0, NT>(blk, lane, L, C, acc_j);      // the hot path: all NT blobs of the lane meet block J
-      } else if (NT == 1 || J == I0) {
-        sym_diag<NT>(blk, lane, L, 0, C);
+      } else if (sym_block_case(I0, J) == 1) {
+        sym_diag<NT>(blk, lane, L, 0, C);                  // J == I0 (for NT == 2 the second blob skips: J < I0 + 1)
       } else {                                             // NT == 2, J == I0 + 1
         sym_block<NT, 0, 1>(blk, lane, L, C, acc_j);
         sym_diag<NT>(blk, lane, L, NT - 1, C);
@@ -633,9 +632,7 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
   if (rows > 0) {
     // rows are triangular (1 .. n_tiles tiles): split them over blockIdx.y until THIS launch (a rank's share of
     // the rows) has at least RMB_WAVES waves of resident CTAs, so that the tail is short
-    int split = (int)((RMB_WAVES * (long)sm_count() * 4 + rows - 1) / rows);
-    if (split > p.n_tiles / 4) split = p.n_tiles / 4;
-    if (split < 1) split = 1;
+    const int split = sym_split_for(rows, (long)sm_count() * 4, RMB_WAVES, p.n_tiles);
     A.n_split = split;
     const dim3 grid((unsigned)rows, (unsigned)split);
     if (c.flags & RMB_NO_TMA) uf_sym_kernel<false, RMB_SYM_NT><<<grid, TPB, 0, c.stream>>>(A);
