@@ -90,9 +90,6 @@ __global__ void prepare_kernel(long n, long n_pad, const double* __restrict__ r,
   T* w = reinterpret_cast<T*>(&o);
 #pragma unroll
   for (int k = 0; k < W; k++) w[k] = T(0);
-  // padding = blobs far away from everything with zero force: the kernels that do evaluate them
-  // (uf_sym_kernel) get finite geometry and exactly zero contributions
-  o.x = T(3.0e7 + 64.0 * (double)(j - n)); o.y = T(3.0e7); o.z = T(3.0e7);
   if (j < n) {
     const double inva = 1.0 / a;
     const double s = scaled ? inva : 1.0;
@@ -325,10 +322,12 @@ __global__ void finish_kernel(const MfArgs<T, (BLOCK == UF_UT) ? 2 : 1> A)
 // (blockIdx.x, scaled by the rank stride) x a range of source tiles
 // (blockIdx.y); rows are triangular (tiles >= the row's own), long rows first.
 // Sums are accumulated with atomics in acc[n_pad][3]; sym_finish_kernel adds the
-// self term, the normalisation and the damping.
+// self term, the normalisation and the damping.  Padding records (zero force) are handled by the TAIL
+// instantiations: a pair with a padding blob is given a finite dummy geometry.
 struct SymArgs {
-  const SrcRec<double, 1>* src;   // n_tiles * TILE records; padding = far-away blobs with zero force
+  const SrcRec<double, 1>* src;   // n_tiles * TILE records; padding = zero force (geometry overridden, see TAIL)
   double* acc;                    // [n_tiles * TILE][3], zeroed before the launch
+  long n;                         // real blobs; records [n, n_tiles * TILE) are zero-force padding
   int n_tiles, n_split;
   int row_first, row_stride;      // row groups handled by this launch: row_first + blockIdx.x * row_stride
   UfCtx<double> K;
@@ -342,9 +341,11 @@ struct SymLane {
 
 // One block J against the lane's blobs k in [K0, K0 + NK): 32 rotation steps, both directions, then the
 // travelling accumulators (home again) are flushed to acc.
-template <int NT, int K0, int NK>
+// TAIL: the block pair touches the zero-force padding past the last real blob; a pair with a padding blob gets a
+// finite dummy geometry, so that it contributes exactly 0 whatever the padding record holds.
+template <int NT, int K0, int NK, bool TAIL>
 __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int lane, SymLane<NT>& L, const UfCtx<double>& C,
-                                          double* __restrict__ acc_j)
+                                          double* __restrict__ acc_j, long n, long i0, long j0)
 {
   typedef double T;
   constexpr int W = 6;
@@ -358,11 +359,14 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
     load_rec<W>(blk + jl * W, w);
 #pragma unroll
     for (int k = K0; k < K0 + NK; k++) {
-      const T rx = L.x[k] - w[0], ry = L.y[k] - w[1], rz = L.h[k] - w[2];
+      T rx = L.x[k] - w[0], ry = L.y[k] - w[1], rz = L.h[k] - w[2];
+      T hi = L.h[k], hj = w[2], hi2 = L.h2[k], hi4 = L.h4[k];
+      if (TAIL && (j0 + jl >= n || i0 + 32 * k + lane >= n)) {
+        rx = T(3); ry = T(0); rz = T(0); hi = T(2); hj = T(2); hi2 = T(4); hi4 = T(8);
+      }
       const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
       const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-      pair_uf_wall_sym<T, true>(rx, ry, rz, L.h[k] + w[2], L.h[k], w[2], L.h2[k], L.h4[k], C, L.f[k], w + 3, any_near,
-                                r2, L.u[k], aj);
+      pair_uf_wall_sym<T, true>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
     }
     // the accumulator of blob j moves to the lane that meets j next
     aj[0] = __shfl_sync(0xffffffffu, aj[0], from);
@@ -374,21 +378,25 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
 }
 
 // Diagonal block (J == the block of blob k): ordered pairs (l, (l + s) & 31), s = 1..31, one direction.
-template <int NT>
+template <int NT, bool TAIL>
 __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lane, SymLane<NT>& L, int k,
-                                         const UfCtx<double>& C)
+                                         const UfCtx<double>& C, long n, long i0)
 {
   typedef double T;
   constexpr int W = 6;
 #pragma unroll 2
   for (int s = 1; s < 32; s++) {
     T w[W];
-    load_rec<W>(blk + ((lane + s) & 31) * W, w);
-    const T rx = L.x[k] - w[0], ry = L.y[k] - w[1], rz = L.h[k] - w[2];
+    const int jl = (lane + s) & 31;
+    load_rec<W>(blk + jl * W, w);
+    T rx = L.x[k] - w[0], ry = L.y[k] - w[1], rz = L.h[k] - w[2];
+    T hi = L.h[k], hj = w[2], hi2 = L.h2[k], hi4 = L.h4[k];
+    if (TAIL && (i0 + jl >= n || i0 + lane >= n)) {
+      rx = T(3); ry = T(0); rz = T(0); hi = T(2); hj = T(2); hi2 = T(4); hi4 = T(8);
+    }
     const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
     const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-    pair_uf_wall_sym<T, false>(rx, ry, rz, L.h[k] + w[2], L.h[k], w[2], L.h2[k], L.h4[k], C, L.f[k], w + 3, any_near, r2,
-                               L.u[k], L.u[k]);
+    pair_uf_wall_sym<T, false>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
   }
 }
 
@@ -456,13 +464,17 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) uf_sym_kernel(const __grid_
       if (sym_block_case(I0, J) == 0) continue;            // J < I0: those pairs of blocks belong to another warp
       const T* blk = tp + jb * 32 * W;
       double* acc_j = A.acc + (size_t)J * 32 * 3;
-      if (sym_block_case(I0 + NT - 1, J) == 2) {
-        sym_block<NT, 0, NT>(blk, lane, L, C, acc_j);      // the hot path: all NT blobs of the lane meet block J
-      } else if (sym_block_case(I0, J) == 1) {
-        sym_diag<NT>(blk, lane, L, 0, C);                  // J == I0 (for NT == 2 the second blob skips: J < I0 + 1)
+      const long i0 = I0 * 32, j0 = J * 32;
+      const bool tail = (j0 + 32 > A.n) || (i0 + 32 * NT > A.n);   // warp-uniform, true for the last blocks only
+      if (sym_block_case(I0 + NT - 1, J) == 2) {           // the hot path: all NT blobs of the lane meet block J
+        if (!tail) sym_block<NT, 0, NT, false>(blk, lane, L, C, acc_j, A.n, i0, j0);
+        else sym_block<NT, 0, NT, true>(blk, lane, L, C, acc_j, A.n, i0, j0);
+      } else if (sym_block_case(I0, J) == 1) {             // J == I0 (for NT == 2 the second blob skips: J < I0 + 1)
+        if (!tail) sym_diag<NT, false>(blk, lane, L, 0, C, A.n, i0);
+        else sym_diag<NT, true>(blk, lane, L, 0, C, A.n, i0);
       } else {                                             // NT == 2, J == I0 + 1
-        sym_block<NT, 0, 1>(blk, lane, L, C, acc_j);
-        sym_diag<NT>(blk, lane, L, NT - 1, C);
+        sym_block<NT, 0, 1, true>(blk, lane, L, C, acc_j, A.n, i0, j0);
+        sym_diag<NT, true>(blk, lane, L, NT - 1, C, A.n, i0 + 32 * (NT - 1));
       }
     }
     __syncthreads();
@@ -624,7 +636,7 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
   cudaError_t e = cudaMemsetAsync(acc, 0, (size_t)n_pad * 3 * sizeof(double), c.stream);
   if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: memset");
   SymArgs A;
-  A.src = rec; A.acc = acc; A.n_tiles = p.n_tiles; A.n_split = p.sym_split;
+  A.src = rec; A.acc = acc; A.n = c.n_src; A.n_tiles = p.n_tiles; A.n_split = p.sym_split;
   A.row_first = row_first; A.row_stride = row_stride;
   A.K = make_uf_ctx<double>(0.0);
   const long rows_all = n_pad / (TPB * RMB_SYM_NT);
