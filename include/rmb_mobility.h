@@ -56,7 +56,7 @@ extern "C" {
 /* flags */
 #define RMB_IN_PLANE 1    /* in_plane_* (mobility.py:255,454,1166,1235): z column and row zero */
 #define RMB_NO_TMA 2      /* stage source tiles with plain loads instead of cp.async.bulk (debug) */
-#define RMB_SYMMETRIC 4   /* single-wall RMB_UF, fp64, open boundaries, n_targets == n_sources: evaluate every
+#define RMB_SYMMETRIC 4   /* RMB_UF (single wall or no wall), fp64, open boundaries, n_targets == n_sources: evaluate every
                              unordered pair once and update both blobs (sums accumulated with atomics: results
                              agree with the row kernel to rounding, but are not bit-reproducible run to run).
                              Without this flag the symmetric kernel is still chosen for eligible calls with

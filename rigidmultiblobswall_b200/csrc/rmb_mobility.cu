@@ -343,7 +343,7 @@ struct SymLane {
 // travelling accumulators (home again) are flushed to acc.
 // TAIL: the block pair touches the zero-force padding past the last real blob; a pair with a padding blob gets a
 // finite dummy geometry, so that it contributes exactly 0 whatever the padding record holds.
-template <int NT, int K0, int NK, bool TAIL>
+template <int NT, int K0, int NK, bool TAIL, bool WALL>
 __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int lane, SymLane<NT>& L, const UfCtx<double>& C,
                                           double* __restrict__ acc_j, long n, long i0, long j0)
 {
@@ -366,7 +366,8 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
       }
       const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
       const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-      pair_uf_wall_sym<T, true>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
+      if (WALL) pair_uf_wall_sym<T, true>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
+      else pair_uf_free_sym<T, true>(rx, ry, rz, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
     }
     // the accumulator of blob j moves to the lane that meets j next
     aj[0] = __shfl_sync(0xffffffffu, aj[0], from);
@@ -378,7 +379,7 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
 }
 
 // Diagonal block (J == the block of blob k): ordered pairs (l, (l + s) & 31), s = 1..31, one direction.
-template <int NT, bool TAIL>
+template <int NT, bool TAIL, bool WALL>
 __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lane, SymLane<NT>& L, int k,
                                          const UfCtx<double>& C, long n, long i0)
 {
@@ -396,11 +397,12 @@ __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lan
     }
     const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
     const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-    pair_uf_wall_sym<T, false>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
+    if (WALL) pair_uf_wall_sym<T, false>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
+    else pair_uf_free_sym<T, false>(rx, ry, rz, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
   }
 }
 
-template <bool TMA, int NT>
+template <bool TMA, int NT, bool WALL>
 __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) uf_sym_kernel(const __grid_constant__ SymArgs A)
 {
   typedef double T;
@@ -467,14 +469,14 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) uf_sym_kernel(const __grid_
       const long i0 = I0 * 32, j0 = J * 32;
       const bool tail = (j0 + 32 > A.n) || (i0 + 32 * NT > A.n);   // warp-uniform, true for the last blocks only
       if (sym_block_case(I0 + NT - 1, J) == 2) {           // the hot path: all NT blobs of the lane meet block J
-        if (!tail) sym_block<NT, 0, NT, false>(blk, lane, L, C, acc_j, A.n, i0, j0);
-        else sym_block<NT, 0, NT, true>(blk, lane, L, C, acc_j, A.n, i0, j0);
+        if (!tail) sym_block<NT, 0, NT, false, WALL>(blk, lane, L, C, acc_j, A.n, i0, j0);
+        else sym_block<NT, 0, NT, true, WALL>(blk, lane, L, C, acc_j, A.n, i0, j0);
       } else if (sym_block_case(I0, J) == 1) {             // J == I0 (for NT == 2 the second blob skips: J < I0 + 1)
-        if (!tail) sym_diag<NT, false>(blk, lane, L, 0, C, A.n, i0);
-        else sym_diag<NT, true>(blk, lane, L, 0, C, A.n, i0);
+        if (!tail) sym_diag<NT, false, WALL>(blk, lane, L, 0, C, A.n, i0);
+        else sym_diag<NT, true, WALL>(blk, lane, L, 0, C, A.n, i0);
       } else {                                             // NT == 2, J == I0 + 1
-        sym_block<NT, 0, 1, true>(blk, lane, L, C, acc_j, A.n, i0, j0);
-        sym_diag<NT, true>(blk, lane, L, NT - 1, C, A.n, i0 + 32 * (NT - 1));
+        sym_block<NT, 0, 1, true, WALL>(blk, lane, L, C, acc_j, A.n, i0, j0);
+        sym_diag<NT, true, WALL>(blk, lane, L, NT - 1, C, A.n, i0 + 32 * (NT - 1));
       }
     }
     __syncthreads();
@@ -488,6 +490,7 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) uf_sym_kernel(const __grid_
 }
 
 // out = B (acc + self term) / (8 pi eta a) for the targets [tgt_off, tgt_off + n_tgt)
+template <bool WALL>
 __global__ void sym_finish_kernel(const SrcRec<double, 1>* __restrict__ src, const double* __restrict__ acc,
                                   const double* __restrict__ damp, long tgt_off, long n_tgt, double norm, int in_plane,
                                   double* __restrict__ out)
@@ -498,7 +501,7 @@ __global__ void sym_finish_kernel(const SrcRec<double, 1>* __restrict__ src, con
   const SrcRec<double, 1>& me = src[gi];
   double sv[3] = {me.v[0], me.v[1], me.v[2]};
   double dx = acc[3 * gi], dy = acc[3 * gi + 1], dz = acc[3 * gi + 2];
-  self_apply<double, UF, true>(me.z, sv, dx, dy, dz);
+  self_apply<double, UF, WALL>(me.z, sv, dx, dy, dz);
   const double sc = norm * damp[gi];
   out[3 * li] = dx * sc;
   out[3 * li + 1] = dy * sc;
@@ -631,8 +634,9 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
   double* damp = reinterpret_cast<double*>(c.ws + p.off_damp);
   const long n_pad = (long)p.n_tiles * TILE;
   const int in_plane = (c.flags & RMB_IN_PLANE) ? 1 : 0;
+  const bool wall = c.wall == RMB_SINGLE_WALL;
   prepare_kernel<double, 1><<<(unsigned)((n_pad + 255) / 256), 256, 0, c.stream>>>(
-      c.n_src, n_pad, c.r, c.va, c.vb, c.a, 1, 1, in_plane, rec, damp);
+      c.n_src, n_pad, c.r, c.va, c.vb, c.a, wall ? 1 : 0, 1, in_plane, rec, damp);
   cudaError_t e = cudaMemsetAsync(acc, 0, (size_t)n_pad * 3 * sizeof(double), c.stream);
   if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: memset");
   SymArgs A;
@@ -647,8 +651,9 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
     const int split = sym_split_for(rows, (long)sm_count() * 4, RMB_WAVES, p.n_tiles);
     A.n_split = split;
     const dim3 grid((unsigned)rows, (unsigned)split);
-    if (c.flags & RMB_NO_TMA) uf_sym_kernel<false, RMB_SYM_NT><<<grid, TPB, 0, c.stream>>>(A);
-    else uf_sym_kernel<true, RMB_SYM_NT><<<grid, TPB, 0, c.stream>>>(A);
+    if (!wall) uf_sym_kernel<true, RMB_SYM_NT, false><<<grid, TPB, 0, c.stream>>>(A);
+    else if (c.flags & RMB_NO_TMA) uf_sym_kernel<false, RMB_SYM_NT, true><<<grid, TPB, 0, c.stream>>>(A);
+    else uf_sym_kernel<true, RMB_SYM_NT, true><<<grid, TPB, 0, c.stream>>>(A);
   }
   e = cudaGetLastError();
   if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: launch");
@@ -661,8 +666,12 @@ int sym_finish(const Call& c, const double* acc)
   const Plan& p = c.plan;
   const SrcRec<double, 1>* rec = reinterpret_cast<const SrcRec<double, 1>*>(c.ws);
   const double* damp = reinterpret_cast<const double*>(c.ws + p.off_damp);
-  sym_finish_kernel<<<(unsigned)((c.n_tgt + 127) / 128), 128, 0, c.stream>>>(
-      rec, acc, damp, c.tgt_off, c.n_tgt, block_norm(UF, c.eta, c.a), (c.flags & RMB_IN_PLANE) ? 1 : 0, c.out);
+  const unsigned nb = (unsigned)((c.n_tgt + 127) / 128);
+  const int in_plane = (c.flags & RMB_IN_PLANE) ? 1 : 0;
+  if (c.wall == RMB_SINGLE_WALL)
+    sym_finish_kernel<true><<<nb, 128, 0, c.stream>>>(rec, acc, damp, c.tgt_off, c.n_tgt, block_norm(UF, c.eta, c.a), in_plane, c.out);
+  else
+    sym_finish_kernel<false><<<nb, 128, 0, c.stream>>>(rec, acc, damp, c.tgt_off, c.n_tgt, block_norm(UF, c.eta, c.a), in_plane, c.out);
   const cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: finish");
   return 0;
@@ -740,7 +749,7 @@ int rmb_launches_per_product(int block, int wall, int precision, int flags, long
   if (block < 0 || block > RMB_UF_UT || n_targets <= 0 || n_sources <= 0) return 0;
   if (make_plan(block, precision, n_targets, n_sources, L, p) != 0) return 0;
   const bool per = L && (L[0] > 0 || L[1] > 0 || L[2] > 0);
-  const bool sym_ok = block == RMB_UF && wall == RMB_SINGLE_WALL && precision == RMB_FP64 && !per &&
+  const bool sym_ok = block == RMB_UF && (wall == RMB_SINGLE_WALL || wall == RMB_NO_WALL) && precision == RMB_FP64 && !per &&
                       n_targets == n_sources;
   const bool sym_want = (flags & RMB_SYMMETRIC) || (!(flags & RMB_DETERMINISTIC) && n_sources >= RMB_SYMMETRIC_MIN_N);
   if (sym_ok && sym_want) return 3;     // prepare_kernel + uf_sym_kernel + sym_finish_kernel (+ one memset)
@@ -776,7 +785,7 @@ int rmb_mobility_product(int block, int wall, int precision, int flags, long n_t
   const bool per = c.L[0] > 0 || c.L[1] > 0 || c.L[2] > 0;
   // pair-symmetric kernel: forced by RMB_SYMMETRIC, chosen by default from RMB_SYMMETRIC_MIN_N blobs on
   // (below that the row kernel is as fast), never with RMB_DETERMINISTIC
-  const bool sym_ok = block == RMB_UF && wall == RMB_SINGLE_WALL && precision == RMB_FP64 && !per &&
+  const bool sym_ok = block == RMB_UF && (wall == RMB_SINGLE_WALL || wall == RMB_NO_WALL) && precision == RMB_FP64 && !per &&
                       n_targets == n_sources && TILE % (TPB * RMB_SYM_NT) == 0;
   const bool sym_want = (flags & RMB_SYMMETRIC) || (!(flags & RMB_DETERMINISTIC) && n_sources >= RMB_SYMMETRIC_MIN_N);
   if (sym_ok && sym_want) return launch_symmetric(c);

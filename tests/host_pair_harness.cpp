@@ -154,7 +154,7 @@ extern "C" void host_st(int wallmode, int fp32, long nt, long ns, const double* 
 }
 
 // ---- pair-symmetric evaluation (pair_uf_wall_sym): every unordered pair once, both directions ----
-extern "C" void host_uf_sym(long n, const double* r, const double* f, double eta, double a, double* out)
+extern "C" void host_uf_sym(int wall, long n, const double* r, const double* f, double eta, double a, double* out)
 {
   typedef double T;
   std::vector<SrcRec<T, 1>> rec(n);
@@ -162,14 +162,22 @@ extern "C" void host_uf_sym(long n, const double* r, const double* f, double eta
   const double inva = 1.0 / a;
   for (long j = 0; j < n; j++) {
     double z = r[3 * j + 2];
-    const double B = (z < a) ? z / a : 1.0;
-    z = (z <= a) ? a : z;
+    const double B = (wall && z < a) ? z / a : 1.0;
+    z = (wall && z <= a) ? a : z;
     damp[j] = B;
     rec[j].x = r[3 * j] * inva; rec[j].y = r[3 * j + 1] * inva; rec[j].z = z * inva;
     for (int c = 0; c < 3; c++) rec[j].v[c] = B * f[3 * j + c];
   }
   for (long i = 0; i < n; i++) {
     const UfCtx<T> C = make_uf_ctx<T>(rec[i].z);
+    if (!wall) {
+      for (long j = i + 1; j < n; j++) {
+        const T rx = rec[i].x - rec[j].x, ry = rec[i].y - rec[j].y, rz = rec[i].z - rec[j].z;
+        const T r2 = rx * rx + ry * ry + rz * rz;
+        pair_uf_free_sym<T, true>(rx, ry, rz, C, rec[i].v, rec[j].v, lt4(r2), r2, &u[3 * i], &u[3 * j]);
+      }
+      continue;
+    }
     for (long j = i + 1; j < n; j++) {
       const T rx = rec[i].x - rec[j].x, ry = rec[i].y - rec[j].y, rz = rec[i].z - rec[j].z;
       const T r2 = rx * rx + ry * ry + rz * rz;
@@ -181,7 +189,8 @@ extern "C" void host_uf_sym(long n, const double* r, const double* f, double eta
   const double norm = block_norm(UF, eta, a);
   for (long i = 0; i < n; i++) {
     T ux = u[3 * i], uy = u[3 * i + 1], uz = u[3 * i + 2];
-    self_apply<T, UF, true>(rec[i].z, rec[i].v, ux, uy, uz);
+    if (wall) self_apply<T, UF, true>(rec[i].z, rec[i].v, ux, uy, uz);
+    else self_apply<T, UF, false>(rec[i].z, rec[i].v, ux, uy, uz);
     out[3 * i] = ux * norm * damp[i]; out[3 * i + 1] = uy * norm * damp[i]; out[3 * i + 2] = uz * norm * damp[i];
   }
 }

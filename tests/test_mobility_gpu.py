@@ -275,3 +275,26 @@ def test_sharded_mobility_single_rank_uses_symmetric_kernel(mb):
     ref = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, flags=mb.DETERMINISTIC)
     assert float(torch.linalg.norm(sm(f) - ref) / torch.linalg.norm(ref)) < 1e-13
     assert not parallel.ShardedMobility(r, eta, a, group=False, periodic_length=np.array([30.0, 0, 0])).symmetric
+
+
+@pytest.mark.parametrize("n", [33, 1000, 3001, 40000])
+def test_symmetric_no_wall(mb, golden, n):
+    """free-space twin of the pair-symmetric kernel (no_wall UF): forced at small n, default at 40000"""
+    import oracle
+    rng = np.random.default_rng(n + 5)
+    a, eta = 0.21, 1.3
+    r = (2.0 + 0.5 * n ** (1 / 3)) * a * rng.random((n, 3)) - 1.0      # no wall: negative heights are legal
+    f = rng.standard_normal((n, 3))
+    out = mb.mobility_product(mb.UF, mb.NO_WALL, r, f, eta, a, flags=mb.SYMMETRIC if n < 20000 else 0)
+    if n <= 3001:
+        assert relerr(out, oracle.mobility_product("UF", "no_wall", r, f, eta, a)) < TOL64
+    else:
+        det = mb.mobility_product(mb.UF, mb.NO_WALL, r, f, eta, a, flags=mb.DETERMINISTIC)
+        assert relerr(out, det) < 1e-13
+        ref = oracle.mobility_product("UF", "no_wall", r, f, eta, a, targets=(777, 777 + 64))
+        assert relerr(out[3 * 777:3 * (777 + 64)], ref) < TOL64
+    for cloud in ("dense", "dilute"):
+        rr, vv = golden[f"{cloud}/r"], golden[f"{cloud}/v"]
+        aa, ee = golden[f"{cloud}/a_eta"]
+        o = mb.mobility_product(mb.UF, mb.NO_WALL, rr, vv, ee, aa, flags=mb.SYMMETRIC)
+        assert relerr(o, golden[f"{cloud}/open/no_wall/UF"]) < TOL64

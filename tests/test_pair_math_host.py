@@ -34,12 +34,12 @@ def harness(tmp_path_factory):
                     p(arrs[3]), p(arrs[4]), eta, p(arrs[5]), p(out))
         return out
 
-    lib.host_uf_sym.argtypes = [ctypes.c_long, dp, dp, ctypes.c_double, ctypes.c_double, dp]
+    lib.host_uf_sym.argtypes = [ctypes.c_int, ctypes.c_long, dp, dp, ctypes.c_double, ctypes.c_double, dp]
 
-    def run_sym(r, f, eta, a):
+    def run_sym(r, f, eta, a, wall=True):
         r = np.ascontiguousarray(r, dtype=np.float64); f = np.ascontiguousarray(f, dtype=np.float64)
         out = np.empty(r.size)
-        lib.host_uf_sym(r.shape[0], r.ctypes.data_as(dp), f.ctypes.data_as(dp), eta, a, out.ctypes.data_as(dp))
+        lib.host_uf_sym(int(wall), r.shape[0], r.ctypes.data_as(dp), f.ctypes.data_as(dp), eta, a, out.ctypes.data_as(dp))
         return out
 
     def run(block, wall, r, va, eta, a, L, fp32=False, in_plane=False, vb=None):
@@ -133,3 +133,5 @@ def test_pair_symmetric_evaluation(golden, harness, cloud):
     r, v = golden[f"{cloud}/r"], golden[f"{cloud}/v"]
     a, eta = golden[f"{cloud}/a_eta"]
     assert relerr(harness.sym(r, v, eta, a), golden[f"{cloud}/open/single_wall/UF"]) < 1e-12
+    if cloud != "c1":
+        assert relerr(harness.sym(r, v, eta, a, wall=False), golden[f"{cloud}/open/no_wall/UF"]) < 1e-12
