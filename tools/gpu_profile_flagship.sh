@@ -2,7 +2,7 @@
 # r01g (1 GPU): tests, smoke, default bench + reference arm, launch list + full ncu capture of the flagship kernel,
 # DRAM traffic of one flagship launch at N = 1M
 mkdir -p gpurun_out
-T=r01g
+T=${1:-r01g}
 echo "== pytest gpu"; timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/${T}_pytest_gpu.log 2>&1; echo "rc=$?"; tail -2 gpurun_out/${T}_pytest_gpu.log
 echo "== smoke"; timeout 300 python __graft_entry__.py smoke > gpurun_out/${T}_smoke.log 2>&1; echo "rc=$?"; tail -3 gpurun_out/${T}_smoke.log
 echo "== bench"; timeout 900 python bench.py > gpurun_out/${T}_bench_1gpu.json 2> gpurun_out/${T}_bench.err; echo "rc=$?"; cat gpurun_out/${T}_bench_1gpu.json
