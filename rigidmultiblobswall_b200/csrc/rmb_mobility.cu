@@ -10,6 +10,9 @@
 //                    (cp.async.bulk + mbarrier, 2 stages); FP64 or FP32
 //   finish_kernel  : O(N n_split) -- sum of source-split partials, self term,
 //                    normalisation, damping B, in-plane mask
+//   uf_sym_kernel  : O(N^2 / 2) -- the flagship (UF, fp64, open boundaries, all
+//                    blobs targets): every unordered pair once, both blobs updated;
+//                    sym_finish_kernel closes it
 // See DESIGN.md for the layout and the roofline.
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -123,7 +126,7 @@ struct MfArgs {
   T inva;
   int n_tiles;       // ceil(n_src / TILE)
   int n_vt;          // = n_tiles (image boxes are looped inside the pair loop)
-  int vt_per_split;  // virtual tiles handled by one blockIdx.y
+  int vt_per_split;  // tiles handled by one blockIdx.y
   int n_split;
   T* partial;        // [n_split][n_tgt][3] when n_split > 1
   double* out;       // [n_tgt][3], written here when n_split == 1
@@ -532,7 +535,7 @@ struct Plan {
 
 // One place decides the decomposition; rmb_workspace_bytes and the launch
 // must agree.  Source splitting (blockIdx.y) is only used when the target
-// blocks alone cannot fill the chip (8 CTAs of 128 threads per SM).
+// blocks alone would give fewer than RMB_WAVES waves of resident CTAs.
 int make_plan(int block, int precision, long n_tgt, long n_src, const double* L, Plan& p)
 {
   const int sms = sm_count();
