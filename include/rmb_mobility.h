@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define RMB_VERSION 101 /* 0.1.1 */
+#define RMB_VERSION 102 /* 0.1.1 */
 
 /* block: which mobility block is applied (mobility.py naming in comments) */
 #define RMB_UF 0    /* *_mobility_trans_times_force        (mobility.py:222,288,1119,1132) */
@@ -111,22 +111,25 @@ int rmb_mobility_product(int block, int wall, int precision, int flags,
                          double *out, void *workspace, size_t workspace_bytes, void *stream);
 
 /*
- * Multi-rank form of the pair-symmetric single-wall UF product (fp64, open boundaries, all n blobs targets
- * and sources).  Every rank calls
+ * Multi-rank form of the pair-symmetric UF product (fp64, wall = RMB_SINGLE_WALL or RMB_NO_WALL, all n blobs
+ * targets and sources, L = NULL or pseudo-periodic in x and/or y only: L[2] must be 0).  Every rank calls
  *   rmb_symmetric_partial()  raw pair sums, for ALL blobs, of this rank's share of the unordered pairs (row groups
  *                            rank, rank + world, ... of the triangular schedule) -> acc, overwritten;
  *                            acc: device, rmb_symmetric_acc_len(n) doubles
  *   [sum acc over the ranks, e.g. ncclAllReduce]
  *   rmb_symmetric_finish()   out = B (acc + self term) / (8 pi eta a) for targets [target_offset, +n_targets);
- *                            same workspace as the partial call (it holds the packed records and the damping)
- * rank = 0, world = 1 is what rmb_mobility_product(RMB_UF, RMB_SINGLE_WALL, RMB_FP64, RMB_SYMMETRIC, ...) does.
- * workspace: >= rmb_workspace_bytes(RMB_UF, RMB_FP64, n, n, NULL).
+ *                            same wall, a, L and workspace as the partial call (the workspace holds the packed
+ *                            records and the damping)
+ * rank = 0, world = 1 is what rmb_mobility_product(RMB_UF, wall, RMB_FP64, RMB_SYMMETRIC, ...) does.
+ * workspace: >= rmb_workspace_bytes(RMB_UF, RMB_FP64, n, n, L).
  */
 size_t rmb_symmetric_acc_len(long n);
-int rmb_symmetric_partial(int flags, long n, int rank, int world, const double *r, const double *force,
-                          double eta, double a, double *acc, void *workspace, size_t workspace_bytes, void *stream);
-int rmb_symmetric_finish(int flags, long n, long target_offset, long n_targets, const double *acc, double eta,
-                         double a, double *out, void *workspace, size_t workspace_bytes, void *stream);
+int rmb_symmetric_partial(int wall, int flags, long n, int rank, int world, const double *r, const double *force,
+                          double eta, double a, const double *L, double *acc, void *workspace,
+                          size_t workspace_bytes, void *stream);
+int rmb_symmetric_finish(int wall, int flags, long n, long target_offset, long n_targets, const double *acc,
+                         double eta, double a, const double *L, double *out, void *workspace,
+                         size_t workspace_bytes, void *stream);
 
 /*
  * Source-target UF product with per-blob radii: the flow at n_targets blobs

@@ -334,6 +334,10 @@ struct SymArgs {
   int n_tiles, n_split;
   int row_first, row_stride;      // row groups handled by this launch: row_first + blockIdx.x * row_stride
   UfCtx<double> K;
+  // PER instantiations only (pseudo-periodic in x and/or y; records then hold unscaled positions)
+  Periodic<double> P;
+  BoxTable<double> box;
+  double inva;
 };
 
 // Registers of one lane: NT blobs, one from each of the warp's NT consecutive blocks.
@@ -346,12 +350,33 @@ struct SymLane {
 // travelling accumulators (home again) are flushed to acc.
 // TAIL: the block pair touches the zero-force padding past the last real blob; a pair with a padding blob gets a
 // finite dummy geometry, so that it contributes exactly 0 whatever the padding record holds.
-template <int NT, int K0, int NK, bool TAIL, bool WALL>
-__device__ __forceinline__ void sym_block(const double* __restrict__ blk, int lane, SymLane<NT>& L, const UfCtx<double>& C,
-                                          double* __restrict__ acc_j, long n, long i0, long j0)
+// PER: pseudo-periodic in x and/or y (never z, so that |R|^2 = r^2 + 4 h_i h_j still holds).  The image boxes are
+// looped innermost; box b seen from i is box -b seen from j (the wrap is odd), so one evaluation with (r, -r)
+// serves both directions and the sum over b covers all boxes of both.
+template <bool PER>
+__device__ __forceinline__ void sym_geometry(const SymArgs& A, double xi, double yi, double hi, const double* w,
+                                             double& rx, double& ry, double& rz, double& hj)
+{
+  rx = xi - w[0]; ry = yi - w[1];
+  if (PER) {
+    if (A.P.per[0]) rx = wrap_shift(rx, A.P.L[0], A.P.invL[0], 0.0);
+    if (A.P.per[1]) ry = wrap_shift(ry, A.P.L[1], A.P.invL[1], 0.0);
+    rx *= A.inva; ry *= A.inva;
+    hj = w[2] * A.inva;
+  } else {
+    hj = w[2];
+  }
+  rz = hi - hj;
+}
+
+template <int NT, int K0, int NK, bool TAIL, bool WALL, bool PER>
+__device__ __forceinline__ void sym_block(const double* __restrict__ blk, int lane, SymLane<NT>& L, const SymArgs& A,
+                                          double* __restrict__ acc_j, long i0, long j0)
 {
   typedef double T;
   constexpr int W = 6;
+  const UfCtx<T>& C = A.K;
+  const long n = A.n;
   T aj[3] = {0, 0, 0};
   int jl = lane;
   const int from = (lane + 1) & 31;
@@ -362,15 +387,28 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
     load_rec<W>(blk + jl * W, w);
 #pragma unroll
     for (int k = K0; k < K0 + NK; k++) {
-      T rx = L.x[k] - w[0], ry = L.y[k] - w[1], rz = L.h[k] - w[2];
-      T hi = L.h[k], hj = w[2], hi2 = L.h2[k], hi4 = L.h4[k];
-      if (TAIL && (j0 + jl >= n || i0 + 32 * k + lane >= n)) {
-        rx = T(3); ry = T(0); rz = T(0); hi = T(2); hj = T(2); hi2 = T(4); hi4 = T(8);
+      T rx, ry, rz, hj;
+      T hi = L.h[k], hi2 = L.h2[k], hi4 = L.h4[k];
+      sym_geometry<PER>(A, L.x[k], L.y[k], hi, w, rx, ry, rz, hj);
+      if (TAIL && (j0 + jl >= n || i0 + 32 * k + lane >= n)) {   // rz = 3: no xy image shift can bring r to 0
+        rx = T(PER ? 0 : 3); ry = T(0); rz = T(PER ? 3 : 0); hi = T(2); hj = T(2); hi2 = T(4); hi4 = T(8);
       }
-      const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
-      const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-      if (WALL) pair_uf_wall_sym<T, true>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
-      else pair_uf_free_sym<T, true>(rx, ry, rz, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
+      if (!PER) {
+        const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
+        const bool any_near = __any_sync(0xffffffffu, lt4(r2));
+        if (WALL) pair_uf_wall_sym<T, true>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
+        else pair_uf_free_sym<T, true>(rx, ry, rz, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
+      } else {
+        const T Rz = hi + hj, rz2 = rz * rz;
+#pragma unroll 1
+        for (int b = 0; b < A.box.n; b++) {
+          const T bx = rx + A.box.s[b][0], by = ry + A.box.s[b][1];
+          const T r2 = RMB_FMA(by, by, RMB_FMA(bx, bx, rz2));
+          const bool any_near = __any_sync(0xffffffffu, lt4(r2));
+          if (WALL) pair_uf_wall_sym<T, true>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
+          else pair_uf_free_sym<T, true>(bx, by, rz, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
+        }
+      }
     }
     // the accumulator of blob j moves to the lane that meets j next
     aj[0] = __shfl_sync(0xffffffffu, aj[0], from);
@@ -382,30 +420,47 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
 }
 
 // Diagonal block (J == the block of blob k): ordered pairs (l, (l + s) & 31), s = 1..31, one direction.
-template <int NT, bool TAIL, bool WALL>
+// PER: also s = 0, the blob's own images in the non-central boxes.
+template <int NT, bool TAIL, bool WALL, bool PER>
 __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lane, SymLane<NT>& L, int k,
-                                         const UfCtx<double>& C, long n, long i0)
+                                         const SymArgs& A, long i0)
 {
   typedef double T;
   constexpr int W = 6;
+  const UfCtx<T>& C = A.K;
+  const long n = A.n;
 #pragma unroll 2
-  for (int s = 1; s < 32; s++) {
+  for (int s = PER ? 0 : 1; s < 32; s++) {
     T w[W];
     const int jl = (lane + s) & 31;
     load_rec<W>(blk + jl * W, w);
-    T rx = L.x[k] - w[0], ry = L.y[k] - w[1], rz = L.h[k] - w[2];
-    T hi = L.h[k], hj = w[2], hi2 = L.h2[k], hi4 = L.h4[k];
+    T rx, ry, rz, hj;
+    T hi = L.h[k], hi2 = L.h2[k], hi4 = L.h4[k];
+    sym_geometry<PER>(A, L.x[k], L.y[k], hi, w, rx, ry, rz, hj);
     if (TAIL && (i0 + jl >= n || i0 + lane >= n)) {
-      rx = T(3); ry = T(0); rz = T(0); hi = T(2); hj = T(2); hi2 = T(4); hi4 = T(8);
+      rx = T(PER ? 0 : 3); ry = T(0); rz = T(PER ? 3 : 0); hi = T(2); hj = T(2); hi2 = T(4); hi4 = T(8);
     }
-    const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
-    const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-    if (WALL) pair_uf_wall_sym<T, false>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
-    else pair_uf_free_sym<T, false>(rx, ry, rz, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
+    if (!PER) {
+      const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
+      const bool any_near = __any_sync(0xffffffffu, lt4(r2));
+      if (WALL) pair_uf_wall_sym<T, false>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
+      else pair_uf_free_sym<T, false>(rx, ry, rz, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
+    } else {
+      const T Rz = hi + hj, rz2 = rz * rz;
+#pragma unroll 1
+      for (int b = 0; b < A.box.n; b++) {
+        if (s == 0 && b == A.box.central) continue;          // the self pair: closed form, added by sym_finish_kernel
+        const T bx = rx + A.box.s[b][0], by = ry + A.box.s[b][1];
+        const T r2 = RMB_FMA(by, by, RMB_FMA(bx, bx, rz2));
+        const bool any_near = __any_sync(0xffffffffu, lt4(r2));
+        if (WALL) pair_uf_wall_sym<T, false>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
+        else pair_uf_free_sym<T, false>(bx, by, rz, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
+      }
+    }
   }
 }
 
-template <bool TMA, int NT, bool WALL>
+template <bool TMA, int NT, bool WALL, bool PER>
 __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) uf_sym_kernel(const __grid_constant__ SymArgs A)
 {
   typedef double T;
@@ -423,13 +478,11 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) uf_sym_kernel(const __grid_
 #pragma unroll
   for (int k = 0; k < NT; k++) {
     const SrcRec<T, 1>& me = A.src[(I0 + k) * 32 + lane];
-    L.x[k] = me.x; L.y[k] = me.y; L.h[k] = me.z;
-    L.h2[k] = 2.0 * me.z; L.h4[k] = 4.0 * me.z;
+    L.x[k] = me.x; L.y[k] = me.y; L.h[k] = PER ? me.z * A.inva : me.z;
+    L.h2[k] = 2.0 * L.h[k]; L.h4[k] = 4.0 * L.h[k];
 #pragma unroll
     for (int c = 0; c < 3; c++) { L.f[k][c] = me.v[c]; L.u[k][c] = 0.0; }
   }
-  const UfCtx<T>& C = A.K;
-
   // this CTA's part of the row's tiles [g * ROW / TILE, n_tiles)
   const SymRowPart part = sym_row_part(g, ROW, TILE, A.n_tiles, (int)blockIdx.y, A.n_split);
   const int v0 = part.v0, v1 = part.v1;
@@ -472,14 +525,14 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) uf_sym_kernel(const __grid_
       const long i0 = I0 * 32, j0 = J * 32;
       const bool tail = (j0 + 32 > A.n) || (i0 + 32 * NT > A.n);   // warp-uniform, true for the last blocks only
       if (sym_block_case(I0 + NT - 1, J) == 2) {           // the hot path: all NT blobs of the lane meet block J
-        if (!tail) sym_block<NT, 0, NT, false, WALL>(blk, lane, L, C, acc_j, A.n, i0, j0);
-        else sym_block<NT, 0, NT, true, WALL>(blk, lane, L, C, acc_j, A.n, i0, j0);
+        if (!tail) sym_block<NT, 0, NT, false, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
+        else sym_block<NT, 0, NT, true, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
       } else if (sym_block_case(I0, J) == 1) {             // J == I0 (for NT == 2 the second blob skips: J < I0 + 1)
-        if (!tail) sym_diag<NT, false, WALL>(blk, lane, L, 0, C, A.n, i0);
-        else sym_diag<NT, true, WALL>(blk, lane, L, 0, C, A.n, i0);
+        if (!tail) sym_diag<NT, false, WALL, PER>(blk, lane, L, 0, A, i0);
+        else sym_diag<NT, true, WALL, PER>(blk, lane, L, 0, A, i0);
       } else {                                             // NT == 2, J == I0 + 1
-        sym_block<NT, 0, 1, true, WALL>(blk, lane, L, C, acc_j, A.n, i0, j0);
-        sym_diag<NT, true, WALL>(blk, lane, L, NT - 1, C, A.n, i0 + 32 * (NT - 1));
+        sym_block<NT, 0, 1, true, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
+        sym_diag<NT, true, WALL, PER>(blk, lane, L, NT - 1, A, i0 + 32 * (NT - 1));
       }
     }
     __syncthreads();
@@ -496,7 +549,7 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) uf_sym_kernel(const __grid_
 template <bool WALL>
 __global__ void sym_finish_kernel(const SrcRec<double, 1>* __restrict__ src, const double* __restrict__ acc,
                                   const double* __restrict__ damp, long tgt_off, long n_tgt, double norm, int in_plane,
-                                  double* __restrict__ out)
+                                  double zscale, double* __restrict__ out)
 {
   const long li = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (li >= n_tgt) return;
@@ -504,7 +557,7 @@ __global__ void sym_finish_kernel(const SrcRec<double, 1>* __restrict__ src, con
   const SrcRec<double, 1>& me = src[gi];
   double sv[3] = {me.v[0], me.v[1], me.v[2]};
   double dx = acc[3 * gi], dy = acc[3 * gi + 1], dz = acc[3 * gi + 2];
-  self_apply<double, UF, WALL>(me.z, sv, dx, dy, dz);
+  self_apply<double, UF, WALL>(me.z * zscale, sv, dx, dy, dz);   // zscale: 1/a when the records are unscaled
   const double sc = norm * damp[gi];
   out[3 * li] = dx * sc;
   out[3 * li + 1] = dy * sc;
@@ -575,6 +628,17 @@ int make_plan(int block, int precision, long n_tgt, long n_src, const double* L,
   return 0;
 }
 
+// The pair-symmetric kernel exists for UF, fp64, wall or no wall, every blob a target, open or pseudo-periodic in
+// x/y (a periodic z breaks |R|^2 = r^2 + 4 h_i h_j).  Forced by RMB_SYMMETRIC, chosen by default from
+// RMB_SYMMETRIC_MIN_N blobs on (below that the row kernel is as fast), never with RMB_DETERMINISTIC.
+bool use_symmetric(int block, int wall, int precision, int flags, long n_tgt, long n_src, const double* L)
+{
+  const bool ok = block == RMB_UF && (wall == RMB_SINGLE_WALL || wall == RMB_NO_WALL) && precision == RMB_FP64 &&
+                  !(L && L[2] > 0) && n_tgt == n_src && TILE % (TPB * RMB_SYM_NT) == 0;
+  const bool want = (flags & RMB_SYMMETRIC) || (!(flags & RMB_DETERMINISTIC) && n_src >= RMB_SYMMETRIC_MIN_N);
+  return ok && want;
+}
+
 struct Call {
   int block, wall, precision, flags;
   long n_tgt, n_src, tgt_off;
@@ -638,14 +702,23 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
   const long n_pad = (long)p.n_tiles * TILE;
   const int in_plane = (c.flags & RMB_IN_PLANE) ? 1 : 0;
   const bool wall = c.wall == RMB_SINGLE_WALL;
+  const bool per = c.L[0] > 0 || c.L[1] > 0;
   prepare_kernel<double, 1><<<(unsigned)((n_pad + 255) / 256), 256, 0, c.stream>>>(
-      c.n_src, n_pad, c.r, c.va, c.vb, c.a, wall ? 1 : 0, 1, in_plane, rec, damp);
+      c.n_src, n_pad, c.r, c.va, c.vb, c.a, wall ? 1 : 0, per ? 0 : 1, in_plane, rec, damp);
   cudaError_t e = cudaMemsetAsync(acc, 0, (size_t)n_pad * 3 * sizeof(double), c.stream);
   if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: memset");
   SymArgs A;
   A.src = rec; A.acc = acc; A.n = c.n_src; A.n_tiles = p.n_tiles; A.n_split = p.sym_split;
   A.row_first = row_first; A.row_stride = row_stride;
   A.K = make_uf_ctx<double>(0.0);
+  A.P.nbox = p.n_boxes;
+  for (int d = 0; d < 3; d++) {
+    A.P.per[d] = d < 2 && c.L[d] > 0;
+    A.P.L[d] = c.L[d];
+    A.P.invL[d] = A.P.per[d] ? 1.0 / c.L[d] : 0.0;
+  }
+  A.inva = 1.0 / c.a;
+  A.box = make_box_table<double>(A.P, 1.0 / c.a);
   const long rows_all = n_pad / (TPB * RMB_SYM_NT);
   const long rows = (rows_all - row_first + row_stride - 1) / row_stride;
   if (rows > 0) {
@@ -654,9 +727,11 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
     const int split = sym_split_for(rows, (long)sm_count() * 4, RMB_WAVES, p.n_tiles);
     A.n_split = split;
     const dim3 grid((unsigned)rows, (unsigned)split);
-    if (!wall) uf_sym_kernel<true, RMB_SYM_NT, false><<<grid, TPB, 0, c.stream>>>(A);
-    else if (c.flags & RMB_NO_TMA) uf_sym_kernel<false, RMB_SYM_NT, true><<<grid, TPB, 0, c.stream>>>(A);
-    else uf_sym_kernel<true, RMB_SYM_NT, true><<<grid, TPB, 0, c.stream>>>(A);
+    if (per && wall) uf_sym_kernel<true, RMB_SYM_NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
+    else if (per) uf_sym_kernel<true, RMB_SYM_NT, false, true><<<grid, TPB, 0, c.stream>>>(A);
+    else if (!wall) uf_sym_kernel<true, RMB_SYM_NT, false, false><<<grid, TPB, 0, c.stream>>>(A);
+    else if (c.flags & RMB_NO_TMA) uf_sym_kernel<false, RMB_SYM_NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
+    else uf_sym_kernel<true, RMB_SYM_NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
   }
   e = cudaGetLastError();
   if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: launch");
@@ -671,10 +746,11 @@ int sym_finish(const Call& c, const double* acc)
   const double* damp = reinterpret_cast<const double*>(c.ws + p.off_damp);
   const unsigned nb = (unsigned)((c.n_tgt + 127) / 128);
   const int in_plane = (c.flags & RMB_IN_PLANE) ? 1 : 0;
+  const double zscale = (c.L[0] > 0 || c.L[1] > 0) ? 1.0 / c.a : 1.0;
   if (c.wall == RMB_SINGLE_WALL)
-    sym_finish_kernel<true><<<nb, 128, 0, c.stream>>>(rec, acc, damp, c.tgt_off, c.n_tgt, block_norm(UF, c.eta, c.a), in_plane, c.out);
+    sym_finish_kernel<true><<<nb, 128, 0, c.stream>>>(rec, acc, damp, c.tgt_off, c.n_tgt, block_norm(UF, c.eta, c.a), in_plane, zscale, c.out);
   else
-    sym_finish_kernel<false><<<nb, 128, 0, c.stream>>>(rec, acc, damp, c.tgt_off, c.n_tgt, block_norm(UF, c.eta, c.a), in_plane, c.out);
+    sym_finish_kernel<false><<<nb, 128, 0, c.stream>>>(rec, acc, damp, c.tgt_off, c.n_tgt, block_norm(UF, c.eta, c.a), in_plane, zscale, c.out);
   const cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: finish");
   return 0;
@@ -751,11 +827,7 @@ int rmb_launches_per_product(int block, int wall, int precision, int flags, long
   Plan p;
   if (block < 0 || block > RMB_UF_UT || n_targets <= 0 || n_sources <= 0) return 0;
   if (make_plan(block, precision, n_targets, n_sources, L, p) != 0) return 0;
-  const bool per = L && (L[0] > 0 || L[1] > 0 || L[2] > 0);
-  const bool sym_ok = block == RMB_UF && (wall == RMB_SINGLE_WALL || wall == RMB_NO_WALL) && precision == RMB_FP64 && !per &&
-                      n_targets == n_sources;
-  const bool sym_want = (flags & RMB_SYMMETRIC) || (!(flags & RMB_DETERMINISTIC) && n_sources >= RMB_SYMMETRIC_MIN_N);
-  if (sym_ok && sym_want) return 3;     // prepare_kernel + uf_sym_kernel + sym_finish_kernel (+ one memset)
+  if (use_symmetric(block, wall, precision, flags, n_targets, n_sources, L)) return 3;     // prepare_kernel + uf_sym_kernel + sym_finish_kernel (+ one memset)
   return 2 + (p.n_split > 1 ? 1 : 0);   // prepare_kernel + mf_kernel (+ finish_kernel when sources are split)
 }
 
@@ -786,12 +858,7 @@ int rmb_mobility_product(int block, int wall, int precision, int flags, long n_t
   if (rc != 0) return rc;
   if (workspace_bytes < c.plan.total) return fail(RMB_E_WORKSPACE, "workspace smaller than rmb_workspace_bytes()");
   const bool per = c.L[0] > 0 || c.L[1] > 0 || c.L[2] > 0;
-  // pair-symmetric kernel: forced by RMB_SYMMETRIC, chosen by default from RMB_SYMMETRIC_MIN_N blobs on
-  // (below that the row kernel is as fast), never with RMB_DETERMINISTIC
-  const bool sym_ok = block == RMB_UF && (wall == RMB_SINGLE_WALL || wall == RMB_NO_WALL) && precision == RMB_FP64 && !per &&
-                      n_targets == n_sources && TILE % (TPB * RMB_SYM_NT) == 0;
-  const bool sym_want = (flags & RMB_SYMMETRIC) || (!(flags & RMB_DETERMINISTIC) && n_sources >= RMB_SYMMETRIC_MIN_N);
-  if (sym_ok && sym_want) return launch_symmetric(c);
+  if (use_symmetric(block, wall, precision, flags, n_targets, n_sources, c.L)) return launch_symmetric(c);
   return precision == RMB_FP32 ? launch_block<float>(c, per) : launch_block<double>(c, per);
 }
 
@@ -800,17 +867,19 @@ size_t rmb_symmetric_acc_len(long n)
   return n <= 0 ? 0 : (size_t)((n + TILE - 1) / TILE) * TILE * 3;
 }
 
-static int sym_call(Call& c, int flags, long n, const double* r, const double* force, double eta, double a,
-                    void* workspace, size_t workspace_bytes, void* stream)
+static int sym_call(Call& c, int wall, int flags, long n, const double* r, const double* force, double eta, double a,
+                    const double* L, void* workspace, size_t workspace_bytes, void* stream)
 {
   if (n <= 0) return fail(RMB_E_ARG, "n must be positive");
+  if (wall != RMB_SINGLE_WALL && wall != RMB_NO_WALL) return fail(RMB_E_ARG, "wall must be RMB_NO_WALL or RMB_SINGLE_WALL");
+  if (L && L[2] > 0) return fail(RMB_E_ARG, "the pair-symmetric product cannot be periodic in z");
   if (!workspace) return fail(RMB_E_ARG, "null device pointer");
   if (!(a > 0) || !(eta > 0)) return fail(RMB_E_ARG, "a and eta must be positive");
   if ((reinterpret_cast<uintptr_t>(workspace) & 15) != 0) return fail(RMB_E_ARG, "workspace must be 16-byte aligned");
-  c.block = RMB_UF; c.wall = RMB_SINGLE_WALL; c.precision = RMB_FP64; c.flags = flags;
+  c.block = RMB_UF; c.wall = wall; c.precision = RMB_FP64; c.flags = flags;
   c.n_tgt = n; c.n_src = n; c.tgt_off = 0;
   c.r = r; c.va = force; c.vb = nullptr; c.eta = eta; c.a = a;
-  for (int d = 0; d < 3; d++) c.L[d] = 0.0;
+  for (int d = 0; d < 3; d++) c.L[d] = L ? L[d] : 0.0;
   c.out = nullptr; c.ws = static_cast<char*>(workspace); c.stream = static_cast<cudaStream_t>(stream);
   const int rc = make_plan(RMB_UF, RMB_FP64, n, n, c.L, c.plan);
   if (rc != 0) return rc;
@@ -818,25 +887,27 @@ static int sym_call(Call& c, int flags, long n, const double* r, const double* f
   return 0;
 }
 
-int rmb_symmetric_partial(int flags, long n, int rank, int world, const double* r, const double* force, double eta,
-                          double a, double* acc, void* workspace, size_t workspace_bytes, void* stream)
+int rmb_symmetric_partial(int wall, int flags, long n, int rank, int world, const double* r, const double* force,
+                          double eta, double a, const double* L, double* acc, void* workspace, size_t workspace_bytes,
+                          void* stream)
 {
   if (world < 1 || rank < 0 || rank >= world) return fail(RMB_E_ARG, "0 <= rank < world required");
   if (!r || !force || !acc) return fail(RMB_E_ARG, "null device pointer");
   Call c;
-  const int rc = sym_call(c, flags, n, r, force, eta, a, workspace, workspace_bytes, stream);
+  const int rc = sym_call(c, wall, flags, n, r, force, eta, a, L, workspace, workspace_bytes, stream);
   return rc != 0 ? rc : sym_partial(c, acc, rank, world);
 }
 
-int rmb_symmetric_finish(int flags, long n, long target_offset, long n_targets, const double* acc, double eta,
-                         double a, double* out, void* workspace, size_t workspace_bytes, void* stream)
+int rmb_symmetric_finish(int wall, int flags, long n, long target_offset, long n_targets, const double* acc,
+                         double eta, double a, const double* L, double* out, void* workspace, size_t workspace_bytes,
+                         void* stream)
 {
   if (target_offset < 0 || n_targets < 0 || target_offset + n_targets > n)
     return fail(RMB_E_ARG, "target range must lie inside [0, n)");
   if (n_targets == 0) return 0;
   if (!acc || !out) return fail(RMB_E_ARG, "null device pointer");
   Call c;
-  const int rc = sym_call(c, flags, n, nullptr, nullptr, eta, a, workspace, workspace_bytes, stream);
+  const int rc = sym_call(c, wall, flags, n, nullptr, nullptr, eta, a, L, workspace, workspace_bytes, stream);
   if (rc != 0) return rc;
   c.tgt_off = target_offset; c.n_tgt = n_targets; c.out = out;
   return sym_finish(c, acc);

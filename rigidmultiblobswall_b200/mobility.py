@@ -137,36 +137,47 @@ def mobility_radii_trans_times_force(r_vectors, force, eta, a, radius_blobs, fun
     return function(r_vectors, r_vectors, force, radius_blobs, radius_blobs, eta, *args, **kwargs)
 
 
-def symmetric_partial(r_vectors, force, eta, a, rank=0, world=1, acc=None, flags=0):
-    """Multi-rank pair-symmetric single-wall UF product, step 1 (rmb_symmetric_partial): this rank's share of
-    the unordered pairs, raw sums for ALL blobs -> acc (device tensor, summed over the ranks by the caller)."""
+def _length3(periodic_length):
+    L = np.zeros(3) if periodic_length is None else np.asarray(
+        periodic_length.cpu() if isinstance(periodic_length, torch.Tensor) else periodic_length, dtype=np.float64)
+    return (ctypes.c_double * 3)(*[float(x) for x in L.reshape(-1)[:3]])
+
+
+def symmetric_partial(r_vectors, force, eta, a, rank=0, world=1, acc=None, flags=0, wall=SINGLE_WALL,
+                      periodic_length=None):
+    """Multi-rank pair-symmetric UF product, step 1 (rmb_symmetric_partial): this rank's share of the unordered
+    pairs, raw sums for ALL blobs -> acc (device tensor, summed over the ranks by the caller).  wall = SINGLE_WALL
+    or NO_WALL; periodic_length may be periodic in x and/or y only."""
     lib = _lib.load()
     dev = _device(r_vectors.device if isinstance(r_vectors, torch.Tensor) else None)
     n = (r_vectors.numel() if isinstance(r_vectors, torch.Tensor) else np.asarray(r_vectors).size) // 3
     with torch.cuda.device(dev):
         r = _as_device_f64(r_vectors, 3 * n, dev)
         f = _as_device_f64(force, 3 * n, dev)
+        Lc = _length3(periodic_length)
         if acc is None:
             acc = torch.empty(lib.rmb_symmetric_acc_len(n), dtype=torch.float64, device=dev)
-        ws = _workspace(lib.rmb_workspace_bytes(UF, FP64, n, n, None), dev)
-        _lib.check(lib.rmb_symmetric_partial(flags | default_flags, n, rank, world, r.data_ptr(), f.data_ptr(),
-                                             float(eta), float(a), acc.data_ptr(), ws.data_ptr(), ws.numel(),
+        ws = _workspace(lib.rmb_workspace_bytes(UF, FP64, n, n, Lc), dev)
+        _lib.check(lib.rmb_symmetric_partial(wall, flags | default_flags, n, rank, world, r.data_ptr(), f.data_ptr(),
+                                             float(eta), float(a), Lc, acc.data_ptr(), ws.data_ptr(), ws.numel(),
                                              torch.cuda.current_stream(dev).cuda_stream))
     return acc
 
 
-def symmetric_finish(n, acc, eta, a, targets=None, out=None, flags=0):
+def symmetric_finish(n, acc, eta, a, targets=None, out=None, flags=0, wall=SINGLE_WALL, periodic_length=None):
     """Step 2 (rmb_symmetric_finish) after the ranks' acc have been summed: self term, normalisation, damping for
-    the target range.  Must follow symmetric_partial on the same device (it reads its workspace)."""
+    the target range.  Must follow symmetric_partial (same wall, a, periodic_length) on the same device: it reads
+    that call's workspace."""
     lib = _lib.load()
     dev = acc.device
     off, cnt = (0, n) if targets is None else targets
     with torch.cuda.device(dev):
         if out is None:
             out = torch.empty(3 * cnt, dtype=torch.float64, device=dev)
-        ws = _workspace(lib.rmb_workspace_bytes(UF, FP64, n, n, None), dev)
-        _lib.check(lib.rmb_symmetric_finish(flags | default_flags, n, off, cnt, acc.data_ptr(), float(eta), float(a),
-                                            out.data_ptr(), ws.data_ptr(), ws.numel(),
+        Lc = _length3(periodic_length)
+        ws = _workspace(lib.rmb_workspace_bytes(UF, FP64, n, n, Lc), dev)
+        _lib.check(lib.rmb_symmetric_finish(wall, flags | default_flags, n, off, cnt, acc.data_ptr(), float(eta),
+                                            float(a), Lc, out.data_ptr(), ws.data_ptr(), ws.numel(),
                                             torch.cuda.current_stream(dev).cuda_stream))
     return out
 

@@ -194,3 +194,60 @@ extern "C" void host_uf_sym(int wall, long n, const double* r, const double* f, 
     out[3 * i] = ux * norm * damp[i]; out[3 * i + 1] = uy * norm * damp[i]; out[3 * i + 2] = uz * norm * damp[i];
   }
 }
+
+// ---- the same with pseudo-periodic images in x / y: per unordered pair the wrap once, then every box with (r, -r);
+// ---- box b seen from i is box -b seen from j, so the loop over b covers all boxes of both directions ----
+extern "C" void host_uf_sym_periodic(int wall, long n, const double* r, const double* f, double eta, double a,
+                                     const double* L, double* out)
+{
+  typedef double T;
+  std::vector<SrcRec<T, 1>> rec(n);     // unscaled positions, as the periodic kernels keep them
+  std::vector<double> damp(n), u(3 * n, 0.0);
+  const double inva = 1.0 / a;
+  for (long j = 0; j < n; j++) {
+    double z = r[3 * j + 2];
+    const double B = (wall && z < a) ? z / a : 1.0;
+    z = (wall && z <= a) ? a : z;
+    damp[j] = B;
+    rec[j].x = r[3 * j]; rec[j].y = r[3 * j + 1]; rec[j].z = z;
+    for (int c = 0; c < 3; c++) rec[j].v[c] = B * f[3 * j + c];
+  }
+  Periodic<T> P;
+  P.nbox = 1;
+  for (int d = 0; d < 3; d++) {
+    P.per[d] = d < 2 && L[d] > 0;
+    P.L[d] = L[d]; P.invL[d] = P.per[d] ? 1.0 / L[d] : 0.0;
+    if (P.per[d]) P.nbox *= 3;
+  }
+  const BoxTable<T> box = make_box_table<T>(P, inva);
+  for (long i = 0; i < n; i++) {
+    const T hi = rec[i].z * inva;
+    const UfCtx<T> C = make_uf_ctx<T>(hi);
+    for (long j = i; j < n; j++) {
+      T rx = rec[i].x - rec[j].x, ry = rec[i].y - rec[j].y;
+      if (P.per[0]) rx = wrap_shift(rx, P.L[0], P.invL[0], T(0));
+      if (P.per[1]) ry = wrap_shift(ry, P.L[1], P.invL[1], T(0));
+      rx *= inva; ry *= inva;
+      const T hj = rec[j].z * inva, rz = hi - hj;
+      for (int b = 0; b < box.n; b++) {
+        if (i == j && b == box.central) continue;
+        const T bx = rx + box.s[b][0], by = ry + box.s[b][1];
+        const T r2 = bx * bx + by * by + rz * rz;
+        if (i == j) {     // own image: one direction (the opposite one is box -b of the same loop)
+          if (wall) pair_uf_wall_sym<T, false>(bx, by, rz, hi + hj, hi, hj, C.ht2, C.ht4, C, rec[i].v, rec[j].v, lt4(r2), r2, &u[3 * i], &u[3 * i]);
+          else pair_uf_free_sym<T, false>(bx, by, rz, C, rec[i].v, rec[j].v, lt4(r2), r2, &u[3 * i], &u[3 * i]);
+        } else {
+          if (wall) pair_uf_wall_sym<T, true>(bx, by, rz, hi + hj, hi, hj, C.ht2, C.ht4, C, rec[i].v, rec[j].v, lt4(r2), r2, &u[3 * i], &u[3 * j]);
+          else pair_uf_free_sym<T, true>(bx, by, rz, C, rec[i].v, rec[j].v, lt4(r2), r2, &u[3 * i], &u[3 * j]);
+        }
+      }
+    }
+  }
+  const double norm = block_norm(UF, eta, a);
+  for (long i = 0; i < n; i++) {
+    T ux = u[3 * i], uy = u[3 * i + 1], uz = u[3 * i + 2];
+    if (wall) self_apply<T, UF, true>(rec[i].z * inva, rec[i].v, ux, uy, uz);
+    else self_apply<T, UF, false>(rec[i].z * inva, rec[i].v, ux, uy, uz);
+    out[3 * i] = ux * norm * damp[i]; out[3 * i + 1] = uy * norm * damp[i]; out[3 * i + 2] = uz * norm * damp[i];
+  }
+}

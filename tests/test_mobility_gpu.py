@@ -3,6 +3,7 @@
  (2) the CPU oracle (oracle/mobility_oracle.c) on seeded inputs,
  (3) size-independent properties at large N.
 Tolerances are BASELINE.json's: 1e-12 relative (fp64), 1e-5 (fp32), norm-wise."""
+import ctypes
 import os
 
 import numpy as np
@@ -274,7 +275,12 @@ def test_sharded_mobility_single_rank_uses_symmetric_kernel(mb):
     assert sm.symmetric
     ref = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, flags=mb.DETERMINISTIC)
     assert float(torch.linalg.norm(sm(f) - ref) / torch.linalg.norm(ref)) < 1e-13
-    assert not parallel.ShardedMobility(r, eta, a, group=False, periodic_length=np.array([30.0, 0, 0])).symmetric
+    Lx = np.array([9.0, 0, 0])
+    smx = parallel.ShardedMobility(r, eta, a, group=False, periodic_length=Lx)
+    assert smx.symmetric
+    refx = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, periodic_length=Lx, flags=mb.DETERMINISTIC)
+    assert float(torch.linalg.norm(smx(f) - refx) / torch.linalg.norm(refx)) < 1e-13
+    assert not parallel.ShardedMobility(r, eta, a, group=False, periodic_length=np.array([9.0, 0, 9.0])).symmetric
 
 
 @pytest.mark.parametrize("n", [33, 1000, 3001, 40000])
@@ -298,3 +304,72 @@ def test_symmetric_no_wall(mb, golden, n):
         aa, ee = golden[f"{cloud}/a_eta"]
         o = mb.mobility_product(mb.UF, mb.NO_WALL, rr, vv, ee, aa, flags=mb.SYMMETRIC)
         assert relerr(o, golden[f"{cloud}/open/no_wall/UF"]) < TOL64
+
+
+# ---- pair-symmetric kernel with pseudo-periodic images in x / y (box b seen from i is box -b seen from j) ----
+@pytest.mark.parametrize("wall", ["single_wall", "no_wall"])
+@pytest.mark.parametrize("lname", ["xy", "x", "xyz"])
+@pytest.mark.parametrize("cloud", ["dense", "dilute"])
+def test_symmetric_periodic_golden(mb, golden, cloud, lname, wall):
+    """xyz (periodic z) is outside the symmetric kernel: the flag must then fall back to the row kernel"""
+    r, v = golden[f"{cloud}/r"], golden[f"{cloud}/v"]
+    a, eta = golden[f"{cloud}/a_eta"]
+    L = golden[f"{cloud}/L_{lname}"]
+    w = mb.SINGLE_WALL if wall == "single_wall" else mb.NO_WALL
+    out = mb.mobility_product(mb.UF, w, r, v, eta, a, periodic_length=L, flags=mb.SYMMETRIC)
+    assert relerr(out, golden[f"{cloud}/{lname}/{wall}/UF"]) < TOL64
+    out = mb.mobility_product(mb.UF, w, r, v, eta, a, periodic_length=L, flags=mb.SYMMETRIC | mb.IN_PLANE)
+    if wall == "single_wall":
+        assert relerr(out, golden[f"{cloud}/{lname}/in_plane/UF"]) < TOL64
+
+
+@pytest.mark.parametrize("n", [1, 31, 33, 255, 257, 1000, 2049])
+@pytest.mark.parametrize("per", [(1, 0), (0, 1), (1, 1)])
+def test_symmetric_periodic_ragged_vs_oracle(mb, n, per):
+    """blobs outside the primary cell (the wrap truncates), overlaps across the cell boundary, blobs below z = a"""
+    import oracle
+    rng = np.random.default_rng(1000 * n + 2 * per[0] + per[1])
+    a, eta = 0.21, 1.3
+    side = (2.0 + 0.3 * n ** (1 / 3)) * a
+    r = side * (1.6 * rng.random((n, 3)) - 0.3)
+    r[:, 2] = side * rng.random(n)
+    f = rng.standard_normal((n, 3))
+    L = np.array([side * per[0], 1.1 * side * per[1], 0.0])
+    for wall, w in (("single_wall", mb.SINGLE_WALL), ("no_wall", mb.NO_WALL)):
+        ref = oracle.mobility_product("UF", wall, r, f, eta, a, periodic_length=L)
+        out = mb.mobility_product(mb.UF, w, r, f, eta, a, periodic_length=L, flags=mb.SYMMETRIC)
+        assert relerr(out, ref) < TOL64
+
+
+def test_symmetric_periodic_large_default_and_multi_rank(mb):
+    """n >= RMB_SYMMETRIC_MIN_N with xy images: the symmetric kernel is the default and agrees with the row kernel;
+    the multi-rank form (world = 3 on one device, sums added by hand) gives the same product"""
+    from rigidmultiblobswall_b200 import _lib
+    lib = _lib.load()
+    rng = np.random.default_rng(31)
+    n, a, eta = 20000, 0.13, 7.0
+    side = (n * 4 * np.pi / 3 / 0.1) ** (1 / 3) * a
+    L = np.array([side, side, 0.0])
+    Lc = (ctypes.c_double * 3)(*L)
+    assert lib.rmb_launches_per_product(mb.UF, mb.SINGLE_WALL, mb.FP64, 0, n, n, Lc) == 3
+    Lz = (ctypes.c_double * 3)(side, 0.0, side)
+    # periodic z: row kernel whatever the flags (its launch count depends on the source split only)
+    assert (lib.rmb_launches_per_product(mb.UF, mb.SINGLE_WALL, mb.FP64, mb.SYMMETRIC, 10 ** 6, 10 ** 6, Lz) ==
+            lib.rmb_launches_per_product(mb.UF, mb.SINGLE_WALL, mb.FP64, mb.DETERMINISTIC, 10 ** 6, 10 ** 6, Lz) == 2)
+    r = torch.from_numpy(side * rng.random((n, 3))).cuda()
+    f = torch.from_numpy(rng.standard_normal((n, 3))).cuda()
+    for w in (mb.SINGLE_WALL, mb.NO_WALL):
+        det = mb.mobility_product(mb.UF, w, r, f, eta, a, periodic_length=L, flags=mb.DETERMINISTIC)
+        sym = mb.mobility_product(mb.UF, w, r, f, eta, a, periodic_length=L)
+        assert float(torch.linalg.norm(sym - det) / torch.linalg.norm(det)) < 1e-13
+        world = 3
+        acc = sum(mb.symmetric_partial(r, f, eta, a, rank=k, world=world, wall=w, periodic_length=L).clone()
+                  for k in range(world))
+        out = torch.cat([mb.symmetric_finish(n, acc, eta, a, targets=t, wall=w, periodic_length=L)
+                         for t in ((0, 9000), (9000, 11000))])
+        assert float(torch.linalg.norm(out - det) / torch.linalg.norm(det)) < 1e-13
+    import oracle
+    ref = oracle.mobility_product("UF", "single_wall", r.cpu().numpy(), f.cpu().numpy(), eta, a, periodic_length=L,
+                                  targets=(5000, 5032))
+    sym = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, periodic_length=L)
+    assert relerr(sym[3 * 5000:3 * 5032].cpu().numpy(), ref) < TOL64

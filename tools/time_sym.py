@@ -1,4 +1,5 @@
-"""Dev tool: default vs pair-symmetric flagship product."""
+"""Dev tool: row kernel (RMB_DETERMINISTIC) vs pair-symmetric kernel; open and pseudo-periodic (xy) boundaries,
+wall and no wall.   python tools/time_sym.py 100000 400000"""
 import sys, os, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -7,16 +8,22 @@ from bench import make_cloud
 res = {}
 for n in [int(x) for x in sys.argv[1:]] or [400000]:
     r, f, a, eta = make_cloud(n)
+    side = float(r[:, :2].max())
     rd, fd = torch.from_numpy(r).cuda().reshape(-1), torch.from_numpy(f).cuda().reshape(-1)
-    for name, fl in (("default", 0), ("symmetric", mb.SYMMETRIC)):
-        for _ in range(2):
-            out = mb.mobility_product(mb.UF, mb.SINGLE_WALL, rd, fd, eta, a, flags=fl)
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(3):
-            out = mb.mobility_product(mb.UF, mb.SINGLE_WALL, rd, fd, eta, a, flags=fl)
-        e1.record(); torch.cuda.synchronize()
-        res["%s_n%d_Gpairs_s" % (name, n)] = n * n / (e0.elapsed_time(e1) / 3) / 1e6
-        res["%s_n%d_norm" % (name, n)] = float(out.norm())
+    for bname, L, boxes in (("open", None, 1), ("xy", np.array([side, side, 0.0]), 9)):
+        for wname, wall in (("wall", mb.SINGLE_WALL), ("nowall", mb.NO_WALL)):
+            outs = {}
+            for name, fl in (("row", mb.DETERMINISTIC), ("symmetric", mb.SYMMETRIC)):
+                reps = 3 if boxes == 1 else 1
+                for _ in range(2):
+                    out = mb.mobility_product(mb.UF, wall, rd, fd, eta, a, periodic_length=L, flags=fl)
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(reps):
+                    out = mb.mobility_product(mb.UF, wall, rd, fd, eta, a, periodic_length=L, flags=fl)
+                e1.record(); torch.cuda.synchronize()
+                res["%s_%s_%s_n%d_Gpairs_s" % (name, bname, wname, n)] = boxes * n * n / (e0.elapsed_time(e1) / reps) / 1e6
+                outs[name] = out
+            res["diff_%s_%s_n%d" % (bname, wname, n)] = float((outs["row"] - outs["symmetric"]).norm() / outs["row"].norm())
 print(json.dumps(res))
