@@ -10,8 +10,9 @@
 //                    (cp.async.bulk + mbarrier, 2 stages); FP64 or FP32
 //   finish_kernel  : O(N n_split) -- sum of source-split partials, self term,
 //                    normalisation, damping B, in-plane mask
-//   uf_sym_kernel  : O(N^2 / 2) -- the flagship (UF, fp64, open boundaries, all
-//                    blobs targets): every unordered pair once, both blobs updated;
+//   uf_sym_kernel  : O(N^2 n_boxes / 2) -- the flagship (UF, fp64, wall or no
+//                    wall, open or pseudo-periodic in x / y, all blobs targets):
+//                    every unordered pair once, both blobs updated;
 //                    sym_finish_kernel closes it
 // See DESIGN.md for the layout and the roofline.
 #include <cuda_runtime.h>
@@ -692,7 +693,7 @@ int launch(const Call& c)
   return 0;
 }
 
-// Pair-symmetric path: single-wall UF, fp64, open boundaries, every blob a target.
+// Pair-symmetric path: UF, fp64, wall or no wall, not periodic in z, every blob a target.
 // Step 1: records + raw pair sums of the row groups row_first, row_first + row_stride, ... into acc.
 int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
 {
