@@ -270,7 +270,7 @@ def run_b200(args):
         solve = gmres_mobility_solve()
 
     if rank == 0:
-        # dominant kernel = uf_sym_kernel<TMA>; one launch per step per rank; the step's other launches
+        # dominant kernel = sym_kernel<UF, TMA>; one launch per step per rank; the step's other launches
         # (L2 flush memset, prepare_kernel, accumulator memset, sym_finish_kernel) are < 0.1% of it
         launch_ms = ms / args.steps
         achieved = (float(n) * n / world * FLOP_PER_PAIR) / (launch_ms * 1e-3) / 1e12   # this rank's share of the pairs

@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define RMB_VERSION 102 /* 0.1.1 */
+#define RMB_VERSION 103 /* 0.1.1 */
 
 /* block: which mobility block is applied (mobility.py naming in comments) */
 #define RMB_UF 0    /* *_mobility_trans_times_force        (mobility.py:222,288,1119,1132) */
@@ -111,23 +111,24 @@ int rmb_mobility_product(int block, int wall, int precision, int flags,
                          double *out, void *workspace, size_t workspace_bytes, void *stream);
 
 /*
- * Multi-rank form of the pair-symmetric UF product (fp64, wall = RMB_SINGLE_WALL or RMB_NO_WALL, all n blobs
- * targets and sources, L = NULL or pseudo-periodic in x and/or y only: L[2] must be 0).  Every rank calls
+ * Multi-rank form of the pair-symmetric product (fp64; block = RMB_UF with wall = RMB_SINGLE_WALL or RMB_NO_WALL,
+ * or block = RMB_UT / RMB_WF / RMB_WT with RMB_SINGLE_WALL; all n blobs targets and sources; L = NULL or
+ * pseudo-periodic in x and/or y only: L[2] must be 0).  Every rank calls
  *   rmb_symmetric_partial()  raw pair sums, for ALL blobs, of this rank's share of the unordered pairs (row groups
  *                            rank, rank + world, ... of the triangular schedule) -> acc, overwritten;
  *                            acc: device, rmb_symmetric_acc_len(n) doubles
  *   [sum acc over the ranks, e.g. ncclAllReduce]
- *   rmb_symmetric_finish()   out = B (acc + self term) / (8 pi eta a) for targets [target_offset, +n_targets);
- *                            same wall, a, L and workspace as the partial call (the workspace holds the packed
+ *   rmb_symmetric_finish()   out = B (acc + self term) / (8 pi eta a^k) for targets [target_offset, +n_targets);
+ *                            same block, wall, a, L and workspace as the partial call (the workspace holds the packed
  *                            records and the damping)
- * rank = 0, world = 1 is what rmb_mobility_product(RMB_UF, wall, RMB_FP64, RMB_SYMMETRIC, ...) does.
- * workspace: >= rmb_workspace_bytes(RMB_UF, RMB_FP64, n, n, L).
+ * rank = 0, world = 1 is what rmb_mobility_product(block, wall, RMB_FP64, RMB_SYMMETRIC, ...) does.
+ * workspace: >= rmb_workspace_bytes(block, RMB_FP64, n, n, L).
  */
 size_t rmb_symmetric_acc_len(long n);
-int rmb_symmetric_partial(int wall, int flags, long n, int rank, int world, const double *r, const double *force,
-                          double eta, double a, const double *L, double *acc, void *workspace,
+int rmb_symmetric_partial(int block, int wall, int flags, long n, int rank, int world, const double *r,
+                          const double *vec, double eta, double a, const double *L, double *acc, void *workspace,
                           size_t workspace_bytes, void *stream);
-int rmb_symmetric_finish(int wall, int flags, long n, long target_offset, long n_targets, const double *acc,
+int rmb_symmetric_finish(int block, int wall, int flags, long n, long target_offset, long n_targets, const double *acc,
                          double eta, double a, const double *L, double *out, void *workspace,
                          size_t workspace_bytes, void *stream);
 

@@ -478,4 +478,127 @@ RMB_HD void self_wt(T h, T tx, T ty, T tz, T& ux, T& uy, T& uz)
   ux = RMB_FMA(mxx, tx, ux); uy = RMB_FMA(mxx, ty, uy); uz = RMB_FMA(mzz, tz, uz);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Pair-symmetric forms of the rotation blocks (single wall, no z wrap).  The (j <- i) interaction is the (i <- j)
+// one with r -> -r and the height that enters the wall term exchanged (WF: the source height, UT: the target
+// height, WT: none), so the reciprocal square roots, q^3, t, k, R_z t and the h-free parts of the polynomials are
+// shared.  The direction helpers take the SIGNED separation (target - source) and kfrz = k_f r_z with that sign.
+template <typename T>
+struct RotShared {
+  T kf, q3, t, Zt, Zt10, ZtH, c12b, kq;   // ZtH = (12 | 6) R_z t for WF | UT; kq = kf - q3
+};
+
+template <typename T, bool IS_WF>
+RMB_HD RotShared<T> rot_shared(T Rz, T hi4, T hj, const UfCtx<T>& C, bool any_near, T r2)
+{
+  RotShared<T> S;
+  S.kf = coupling_k(r2, any_near, C);
+  const T q = rsqrt_full(RMB_FMA(hi4, hj, r2), C.c38, C.khalf);
+  S.t = q * q;
+  S.Zt = Rz * S.t;
+  S.q3 = q * S.t;
+  const T k = Rz * S.Zt;
+  S.Zt10 = T(10.0) * S.Zt;
+  S.ZtH = (IS_WF ? C.k12 : T(6.0)) * S.Zt;
+  S.c12b = RMB_FMA(RMB_FMA(IS_WF ? C.km20 : C.km10, k, C.k2), S.t, C.k1);
+  S.kq = S.kf - S.q3;
+  return S;
+}
+
+// w += M_WF(r, source height h) f      (pair_wf, wall)
+template <typename T>
+RMB_HD void wf_direction(T rx, T ry, T rz, T Rz, T h, T kfrz, const T* f, const RotShared<T>& S, T* w)
+{
+  const T Rf = RMB_FMA(Rz, f[2], RMB_FMA(ry, f[1], rx * f[0]));
+  const T E = (RMB_FMA(T(-6.0), h, S.Zt10) * S.t) * Rf;
+  const T c14 = RMB_FMA(T(2.0), S.Zt, rz);
+  const T c12 = RMB_FMA(h, S.ZtH, S.c12b);
+  const T D = RMB_FMA(c12, f[2], E);
+  const T P1 = RMB_FMA(-S.q3, c14, kfrz);
+  const T P2 = RMB_FMA(-S.q3, D, S.kf * f[2]);
+  const T cz = RMB_FMA(ry, f[0], -(rx * f[1]));
+  w[0] = RMB_FMA(f[1], P1, w[0]); w[0] = RMB_FMA(-ry, P2, w[0]);
+  w[1] = RMB_FMA(-f[0], P1, w[1]); w[1] = RMB_FMA(rx, P2, w[1]);
+  w[2] = RMB_FMA(S.kq, cz, w[2]);
+}
+
+// u += M_UT(r, target height h) tau    (pair_ut, wall)
+template <typename T>
+RMB_HD void ut_direction(T rx, T ry, T rz, T h, T kfrz, const T* tq, const RotShared<T>& S, T* u)
+{
+  const T cz = RMB_FMA(rx, tq[1], -(ry * tq[0]));
+  const T E = (RMB_FMA(T(-6.0), h, S.Zt10) * S.t) * cz;
+  const T c14 = RMB_FMA(T(2.0), S.Zt, -rz);
+  const T c12 = RMB_FMA(h, S.ZtH, S.c12b);
+  const T P1 = RMB_FMA(S.q3, c14, kfrz);
+  const T dt = S.kq * tq[2];
+  const T qE = S.q3 * E;
+  u[0] = RMB_FMA(tq[1], P1, u[0]); u[0] = RMB_FMA(-ry, dt, u[0]); u[0] = RMB_FMA(-qE, rx, u[0]);
+  u[1] = RMB_FMA(-tq[0], P1, u[1]); u[1] = RMB_FMA(rx, dt, u[1]); u[1] = RMB_FMA(-qE, ry, u[1]);
+  u[2] = RMB_FMA(cz, RMB_FMA(S.q3, c12, -S.kf), u[2]);
+}
+
+template <typename T, bool BOTH>
+RMB_HD void pair_wf_wall_sym(T rx, T ry, T rz, T Rz, T hi, T hj, T hi4, const UfCtx<T>& C, const T* fi, const T* fj,
+                             bool any_near, T r2, T* wi, T* wj)
+{
+  const RotShared<T> S = rot_shared<T, true>(Rz, hi4, hj, C, any_near, r2);
+  const T kfrz = S.kf * rz;
+  wf_direction<T>(rx, ry, rz, Rz, hj, kfrz, fj, S, wi);
+  if (BOTH) wf_direction<T>(-rx, -ry, -rz, Rz, hi, -kfrz, fi, S, wj);
+}
+
+template <typename T, bool BOTH>
+RMB_HD void pair_ut_wall_sym(T rx, T ry, T rz, T Rz, T hi, T hj, T hi4, const UfCtx<T>& C, const T* ti, const T* tj,
+                             bool any_near, T r2, T* ui, T* uj)
+{
+  const RotShared<T> S = rot_shared<T, false>(Rz, hi4, hj, C, any_near, r2);
+  const T kfrz = S.kf * rz;
+  ut_direction<T>(rx, ry, rz, hi, kfrz, tj, S, ui);
+  if (BOTH) ut_direction<T>(-rx, -ry, -rz, hj, -kfrz, ti, S, uj);
+}
+
+// w += M_WT(r) tau for one direction; everything that does not contain the torque is shared (the wall term of WT
+// has no height in it besides R_z)
+template <typename T>
+RMB_HD void wt_direction(T rx, T ry, T rz, T Rz, T Aa, T Bc, T q5a, T q5b, const T* tq, T* w)
+{
+  const T s = RMB_FMA(ry, tq[1], rx * tq[0]);
+  const T B = Bc * RMB_FMA(rz, tq[2], s);
+  const T m1 = q5a * RMB_FMA(Rz, tq[2], s);
+  const T m2 = q5b * RMB_FMA(rx, tq[1], -(ry * tq[0]));
+  const T Bm = B + m1;
+  w[0] = RMB_FMA(Aa, tq[0], w[0]); w[0] = RMB_FMA(Bm, rx, w[0]); w[0] = RMB_FMA(-m2, ry, w[0]);
+  w[1] = RMB_FMA(Aa, tq[1], w[1]); w[1] = RMB_FMA(Bm, ry, w[1]); w[1] = RMB_FMA(m2, rx, w[1]);
+  w[2] = RMB_FMA(Aa, tq[2], w[2]); w[2] = RMB_FMA(B, rz, w[2]); w[2] = RMB_FMA(-m1, Rz, w[2]);
+}
+
+template <typename T, bool BOTH>
+RMB_HD void pair_wt_wall_sym(T rx, T ry, T rz, T Rz, T hi4, T hj, const UfCtx<T>& C, const T* ti, const T* tj,
+                             bool any_near, T r2, T* wi, T* wj)
+{
+  const T invr = rsqrt_full(r2, C.c38, C.khalf);
+  const T invr2 = invr * invr;
+  const T invr3 = invr2 * invr;
+  T A = T(-0.5) * invr3;
+  T Bc = (T(1.5) * invr2) * invr3;
+  if (any_near) {
+    const T r = r2 * invr;
+    const T An = RMB_FMA(RMB_FMA(T(0.078125), r2, T(-0.84375)), r, T(1.0));
+    const T Bn = RMB_FMA(T(-0.046875), r, T(0.28125) * invr);
+    const bool near = lt4(r2);
+    A = near ? An : A;
+    Bc = near ? Bn : Bc;
+  }
+  const T q = rsqrt_full(RMB_FMA(hi4, hj, r2), C.c38, C.khalf);
+  const T t = q * q;
+  const T q3 = q * t;
+  const T k = (Rz * Rz) * t;
+  const T q5 = q3 * t;
+  const T Aa = RMB_FMA(RMB_FMA(C.km3, k, C.khalf), q3, A);
+  const T q5a = T(-1.5) * q5, q5b = T(3.0) * q5;
+  wt_direction<T>(rx, ry, rz, Rz, Aa, Bc, q5a, q5b, tj, wi);
+  if (BOTH) wt_direction<T>(-rx, -ry, -rz, Rz, Aa, Bc, q5a, q5b, ti, wj);
+}
+
 }  // namespace rmb

@@ -10,7 +10,8 @@
 //                    (cp.async.bulk + mbarrier, 2 stages); FP64 or FP32
 //   finish_kernel  : O(N n_split) -- sum of source-split partials, self term,
 //                    normalisation, damping B, in-plane mask
-//   uf_sym_kernel  : O(N^2 n_boxes / 2) -- the flagship (UF, fp64, wall or no
+//   sym_kernel     : O(N^2 n_boxes / 2) -- the flagship (UF and, with a wall,
+//                    UT / WF / WT; fp64, wall or no
 //                    wall, open or pseudo-periodic in x / y, all blobs targets):
 //                    every unordered pair once, both blobs updated;
 //                    sym_finish_kernel closes it
@@ -354,6 +355,25 @@ struct SymLane {
 // PER: pseudo-periodic in x and/or y (never z, so that |R|^2 = r^2 + 4 h_i h_j still holds).  The image boxes are
 // looped innermost; box b seen from i is box -b seen from j (the wrap is odd), so one evaluation with (r, -r)
 // serves both directions and the sum over b covers all boxes of both.
+// One unordered pair of block BLOCK: u_i += M_ij v_j and (BOTH) u_j += M_ji v_i from shared factors (pair_math.cuh).
+template <int BLOCK, bool WALL, bool BOTH>
+__device__ __forceinline__ void sym_pair(double rx, double ry, double rz, double Rz, double hi, double hj, double hi2,
+                                         double hi4, const UfCtx<double>& C, const double* vi, const double* vj,
+                                         bool any_near, double r2, double* ui, double* uj)
+{
+  typedef double T;
+  if (BLOCK == UF) {
+    if (WALL) pair_uf_wall_sym<T, BOTH>(rx, ry, rz, Rz, hi, hj, hi2, hi4, C, vi, vj, any_near, r2, ui, uj);
+    else pair_uf_free_sym<T, BOTH>(rx, ry, rz, C, vi, vj, any_near, r2, ui, uj);
+  } else if (BLOCK == WF) {
+    pair_wf_wall_sym<T, BOTH>(rx, ry, rz, Rz, hi, hj, hi4, C, vi, vj, any_near, r2, ui, uj);
+  } else if (BLOCK == UT) {
+    pair_ut_wall_sym<T, BOTH>(rx, ry, rz, Rz, hi, hj, hi4, C, vi, vj, any_near, r2, ui, uj);
+  } else {
+    pair_wt_wall_sym<T, BOTH>(rx, ry, rz, Rz, hi4, hj, C, vi, vj, any_near, r2, ui, uj);
+  }
+}
+
 template <bool PER>
 __device__ __forceinline__ void sym_geometry(const SymArgs& A, double xi, double yi, double hi, const double* w,
                                              double& rx, double& ry, double& rz, double& hj)
@@ -370,7 +390,7 @@ __device__ __forceinline__ void sym_geometry(const SymArgs& A, double xi, double
   rz = hi - hj;
 }
 
-template <int NT, int K0, int NK, bool TAIL, bool WALL, bool PER>
+template <int BLOCK, int NT, int K0, int NK, bool TAIL, bool WALL, bool PER>
 __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int lane, SymLane<NT>& L, const SymArgs& A,
                                           double* __restrict__ acc_j, long i0, long j0)
 {
@@ -397,8 +417,7 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
       if (!PER) {
         const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
         const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-        if (WALL) pair_uf_wall_sym<T, true>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
-        else pair_uf_free_sym<T, true>(rx, ry, rz, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
+        sym_pair<BLOCK, WALL, true>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
       } else {
         const T Rz = hi + hj, rz2 = rz * rz;
 #pragma unroll 1
@@ -406,8 +425,7 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
           const T bx = rx + A.box.s[b][0], by = ry + A.box.s[b][1];
           const T r2 = RMB_FMA(by, by, RMB_FMA(bx, bx, rz2));
           const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-          if (WALL) pair_uf_wall_sym<T, true>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
-          else pair_uf_free_sym<T, true>(bx, by, rz, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
+          sym_pair<BLOCK, WALL, true>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
         }
       }
     }
@@ -422,7 +440,7 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
 
 // Diagonal block (J == the block of blob k): ordered pairs (l, (l + s) & 31), s = 1..31, one direction.
 // PER: also s = 0, the blob's own images in the non-central boxes.
-template <int NT, bool TAIL, bool WALL, bool PER>
+template <int BLOCK, int NT, bool TAIL, bool WALL, bool PER>
 __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lane, SymLane<NT>& L, int k,
                                          const SymArgs& A, long i0)
 {
@@ -444,8 +462,7 @@ __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lan
     if (!PER) {
       const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
       const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-      if (WALL) pair_uf_wall_sym<T, false>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
-      else pair_uf_free_sym<T, false>(rx, ry, rz, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
+      sym_pair<BLOCK, WALL, false>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
     } else {
       const T Rz = hi + hj, rz2 = rz * rz;
 #pragma unroll 1
@@ -454,15 +471,14 @@ __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lan
         const T bx = rx + A.box.s[b][0], by = ry + A.box.s[b][1];
         const T r2 = RMB_FMA(by, by, RMB_FMA(bx, bx, rz2));
         const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-        if (WALL) pair_uf_wall_sym<T, false>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
-        else pair_uf_free_sym<T, false>(bx, by, rz, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
+        sym_pair<BLOCK, WALL, false>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
       }
     }
   }
 }
 
-template <bool TMA, int NT, bool WALL, bool PER>
-__global__ void __launch_bounds__(TPB, RMB_SYM_MINB) uf_sym_kernel(const __grid_constant__ SymArgs A)
+template <int BLOCK, bool TMA, int NT, bool WALL, bool PER>
+__global__ void __launch_bounds__(TPB, RMB_SYM_MINB) sym_kernel(const __grid_constant__ SymArgs A)
 {
   typedef double T;
   constexpr int W = 6;
@@ -526,14 +542,14 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) uf_sym_kernel(const __grid_
       const long i0 = I0 * 32, j0 = J * 32;
       const bool tail = (j0 + 32 > A.n) || (i0 + 32 * NT > A.n);   // warp-uniform, true for the last blocks only
       if (sym_block_case(I0 + NT - 1, J) == 2) {           // the hot path: all NT blobs of the lane meet block J
-        if (!tail) sym_block<NT, 0, NT, false, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
-        else sym_block<NT, 0, NT, true, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
+        if (!tail) sym_block<BLOCK, NT, 0, NT, false, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
+        else sym_block<BLOCK, NT, 0, NT, true, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
       } else if (sym_block_case(I0, J) == 1) {             // J == I0 (for NT == 2 the second blob skips: J < I0 + 1)
-        if (!tail) sym_diag<NT, false, WALL, PER>(blk, lane, L, 0, A, i0);
-        else sym_diag<NT, true, WALL, PER>(blk, lane, L, 0, A, i0);
+        if (!tail) sym_diag<BLOCK, NT, false, WALL, PER>(blk, lane, L, 0, A, i0);
+        else sym_diag<BLOCK, NT, true, WALL, PER>(blk, lane, L, 0, A, i0);
       } else {                                             // NT == 2, J == I0 + 1
-        sym_block<NT, 0, 1, true, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
-        sym_diag<NT, true, WALL, PER>(blk, lane, L, NT - 1, A, i0 + 32 * (NT - 1));
+        sym_block<BLOCK, NT, 0, 1, true, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
+        sym_diag<BLOCK, NT, true, WALL, PER>(blk, lane, L, NT - 1, A, i0 + 32 * (NT - 1));
       }
     }
     __syncthreads();
@@ -547,7 +563,7 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) uf_sym_kernel(const __grid_
 }
 
 // out = B (acc + self term) / (8 pi eta a) for the targets [tgt_off, tgt_off + n_tgt)
-template <bool WALL>
+template <int BLOCK, bool WALL>
 __global__ void sym_finish_kernel(const SrcRec<double, 1>* __restrict__ src, const double* __restrict__ acc,
                                   const double* __restrict__ damp, long tgt_off, long n_tgt, double norm, int in_plane,
                                   double zscale, double* __restrict__ out)
@@ -558,7 +574,7 @@ __global__ void sym_finish_kernel(const SrcRec<double, 1>* __restrict__ src, con
   const SrcRec<double, 1>& me = src[gi];
   double sv[3] = {me.v[0], me.v[1], me.v[2]};
   double dx = acc[3 * gi], dy = acc[3 * gi + 1], dz = acc[3 * gi + 2];
-  self_apply<double, UF, WALL>(me.z * zscale, sv, dx, dy, dz);   // zscale: 1/a when the records are unscaled
+  self_apply<double, BLOCK, WALL>(me.z * zscale, sv, dx, dy, dz);   // zscale: 1/a when the records are unscaled
   const double sc = norm * damp[gi];
   out[3 * li] = dx * sc;
   out[3 * li + 1] = dy * sc;
@@ -584,7 +600,7 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 struct Plan {
   int n_tiles, n_boxes, n_vt, n_split, vt_per_split, tgt_blocks;
   size_t rec_bytes, off_damp, off_partial, off_acc, total;
-  int sym_split;   // blockIdx.y extent of uf_sym_kernel
+  int sym_split;   // blockIdx.y extent of sym_kernel
 };
 
 // One place decides the decomposition; rmb_workspace_bytes and the launch
@@ -629,12 +645,14 @@ int make_plan(int block, int precision, long n_tgt, long n_src, const double* L,
   return 0;
 }
 
-// The pair-symmetric kernel exists for UF, fp64, wall or no wall, every blob a target, open or pseudo-periodic in
-// x/y (a periodic z breaks |R|^2 = r^2 + 4 h_i h_j).  Forced by RMB_SYMMETRIC, chosen by default from
+// The pair-symmetric kernel exists for UF (wall or no wall) and UT / WF / WT (wall), fp64, every blob a target, open
+// or pseudo-periodic in x/y (a periodic z breaks |R|^2 = r^2 + 4 h_i h_j).  Forced by RMB_SYMMETRIC, chosen by default from
 // RMB_SYMMETRIC_MIN_N blobs on (below that the row kernel is as fast), never with RMB_DETERMINISTIC.
 bool use_symmetric(int block, int wall, int precision, int flags, long n_tgt, long n_src, const double* L)
 {
-  const bool ok = block == RMB_UF && (wall == RMB_SINGLE_WALL || wall == RMB_NO_WALL) && precision == RMB_FP64 &&
+  const bool blk = (block == RMB_UF && (wall == RMB_SINGLE_WALL || wall == RMB_NO_WALL)) ||
+                   ((block == RMB_UT || block == RMB_WF || block == RMB_WT) && wall == RMB_SINGLE_WALL);
+  const bool ok = blk && precision == RMB_FP64 &&
                   !(L && L[2] > 0) && n_tgt == n_src && TILE % (TPB * RMB_SYM_NT) == 0;
   const bool want = (flags & RMB_SYMMETRIC) || (!(flags & RMB_DETERMINISTIC) && n_src >= RMB_SYMMETRIC_MIN_N);
   return ok && want;
@@ -728,11 +746,21 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
     const int split = sym_split_for(rows, (long)sm_count() * 4, RMB_WAVES, p.n_tiles);
     A.n_split = split;
     const dim3 grid((unsigned)rows, (unsigned)split);
-    if (per && wall) uf_sym_kernel<true, RMB_SYM_NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
-    else if (per) uf_sym_kernel<true, RMB_SYM_NT, false, true><<<grid, TPB, 0, c.stream>>>(A);
-    else if (!wall) uf_sym_kernel<true, RMB_SYM_NT, false, false><<<grid, TPB, 0, c.stream>>>(A);
-    else if (c.flags & RMB_NO_TMA) uf_sym_kernel<false, RMB_SYM_NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
-    else uf_sym_kernel<true, RMB_SYM_NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
+    constexpr int NT = RMB_SYM_NT;
+    if (c.block == RMB_UT) {
+      if (per) sym_kernel<UT, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
+      else sym_kernel<UT, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
+    } else if (c.block == RMB_WF) {
+      if (per) sym_kernel<WF, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
+      else sym_kernel<WF, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
+    } else if (c.block == RMB_WT) {
+      if (per) sym_kernel<WT, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
+      else sym_kernel<WT, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
+    } else if (per && wall) sym_kernel<UF, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
+    else if (per) sym_kernel<UF, true, NT, false, true><<<grid, TPB, 0, c.stream>>>(A);
+    else if (!wall) sym_kernel<UF, true, NT, false, false><<<grid, TPB, 0, c.stream>>>(A);
+    else if (c.flags & RMB_NO_TMA) sym_kernel<UF, false, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
+    else sym_kernel<UF, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
   }
   e = cudaGetLastError();
   if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: launch");
@@ -748,10 +776,14 @@ int sym_finish(const Call& c, const double* acc)
   const unsigned nb = (unsigned)((c.n_tgt + 127) / 128);
   const int in_plane = (c.flags & RMB_IN_PLANE) ? 1 : 0;
   const double zscale = (c.L[0] > 0 || c.L[1] > 0) ? 1.0 / c.a : 1.0;
-  if (c.wall == RMB_SINGLE_WALL)
-    sym_finish_kernel<true><<<nb, 128, 0, c.stream>>>(rec, acc, damp, c.tgt_off, c.n_tgt, block_norm(UF, c.eta, c.a), in_plane, zscale, c.out);
-  else
-    sym_finish_kernel<false><<<nb, 128, 0, c.stream>>>(rec, acc, damp, c.tgt_off, c.n_tgt, block_norm(UF, c.eta, c.a), in_plane, zscale, c.out);
+  const double norm = block_norm(c.block, c.eta, c.a);
+#define RMB_SYM_FINISH(B, W) sym_finish_kernel<B, W><<<nb, 128, 0, c.stream>>>(rec, acc, damp, c.tgt_off, c.n_tgt, norm, in_plane, zscale, c.out)
+  if (c.block == RMB_UT) RMB_SYM_FINISH(UT, true);
+  else if (c.block == RMB_WF) RMB_SYM_FINISH(WF, true);
+  else if (c.block == RMB_WT) RMB_SYM_FINISH(WT, true);
+  else if (c.wall == RMB_SINGLE_WALL) RMB_SYM_FINISH(UF, true);
+  else RMB_SYM_FINISH(UF, false);
+#undef RMB_SYM_FINISH
   const cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: finish");
   return 0;
@@ -828,7 +860,7 @@ int rmb_launches_per_product(int block, int wall, int precision, int flags, long
   Plan p;
   if (block < 0 || block > RMB_UF_UT || n_targets <= 0 || n_sources <= 0) return 0;
   if (make_plan(block, precision, n_targets, n_sources, L, p) != 0) return 0;
-  if (use_symmetric(block, wall, precision, flags, n_targets, n_sources, L)) return 3;     // prepare_kernel + uf_sym_kernel + sym_finish_kernel (+ one memset)
+  if (use_symmetric(block, wall, precision, flags, n_targets, n_sources, L)) return 3;     // prepare_kernel + sym_kernel + sym_finish_kernel (+ one memset)
   return 2 + (p.n_split > 1 ? 1 : 0);   // prepare_kernel + mf_kernel (+ finish_kernel when sources are split)
 }
 
@@ -868,38 +900,40 @@ size_t rmb_symmetric_acc_len(long n)
   return n <= 0 ? 0 : (size_t)((n + TILE - 1) / TILE) * TILE * 3;
 }
 
-static int sym_call(Call& c, int wall, int flags, long n, const double* r, const double* force, double eta, double a,
+static int sym_call(Call& c, int block, int wall, int flags, long n, const double* r, const double* force, double eta, double a,
                     const double* L, void* workspace, size_t workspace_bytes, void* stream)
 {
   if (n <= 0) return fail(RMB_E_ARG, "n must be positive");
-  if (wall != RMB_SINGLE_WALL && wall != RMB_NO_WALL) return fail(RMB_E_ARG, "wall must be RMB_NO_WALL or RMB_SINGLE_WALL");
+  if (block < RMB_UF || block > RMB_WT) return fail(RMB_E_ARG, "block must be RMB_UF, RMB_UT, RMB_WF or RMB_WT");
+  if (wall != RMB_SINGLE_WALL && !(wall == RMB_NO_WALL && block == RMB_UF))
+    return fail(RMB_E_ARG, "the pair-symmetric product exists for RMB_SINGLE_WALL (all blocks) and RMB_NO_WALL (RMB_UF)");
   if (L && L[2] > 0) return fail(RMB_E_ARG, "the pair-symmetric product cannot be periodic in z");
   if (!workspace) return fail(RMB_E_ARG, "null device pointer");
   if (!(a > 0) || !(eta > 0)) return fail(RMB_E_ARG, "a and eta must be positive");
   if ((reinterpret_cast<uintptr_t>(workspace) & 15) != 0) return fail(RMB_E_ARG, "workspace must be 16-byte aligned");
-  c.block = RMB_UF; c.wall = wall; c.precision = RMB_FP64; c.flags = flags;
+  c.block = block; c.wall = wall; c.precision = RMB_FP64; c.flags = flags;
   c.n_tgt = n; c.n_src = n; c.tgt_off = 0;
   c.r = r; c.va = force; c.vb = nullptr; c.eta = eta; c.a = a;
   for (int d = 0; d < 3; d++) c.L[d] = L ? L[d] : 0.0;
   c.out = nullptr; c.ws = static_cast<char*>(workspace); c.stream = static_cast<cudaStream_t>(stream);
-  const int rc = make_plan(RMB_UF, RMB_FP64, n, n, c.L, c.plan);
+  const int rc = make_plan(block, RMB_FP64, n, n, c.L, c.plan);
   if (rc != 0) return rc;
   if (workspace_bytes < c.plan.total) return fail(RMB_E_WORKSPACE, "workspace smaller than rmb_workspace_bytes()");
   return 0;
 }
 
-int rmb_symmetric_partial(int wall, int flags, long n, int rank, int world, const double* r, const double* force,
+int rmb_symmetric_partial(int block, int wall, int flags, long n, int rank, int world, const double* r, const double* force,
                           double eta, double a, const double* L, double* acc, void* workspace, size_t workspace_bytes,
                           void* stream)
 {
   if (world < 1 || rank < 0 || rank >= world) return fail(RMB_E_ARG, "0 <= rank < world required");
   if (!r || !force || !acc) return fail(RMB_E_ARG, "null device pointer");
   Call c;
-  const int rc = sym_call(c, wall, flags, n, r, force, eta, a, L, workspace, workspace_bytes, stream);
+  const int rc = sym_call(c, block, wall, flags, n, r, force, eta, a, L, workspace, workspace_bytes, stream);
   return rc != 0 ? rc : sym_partial(c, acc, rank, world);
 }
 
-int rmb_symmetric_finish(int wall, int flags, long n, long target_offset, long n_targets, const double* acc,
+int rmb_symmetric_finish(int block, int wall, int flags, long n, long target_offset, long n_targets, const double* acc,
                          double eta, double a, const double* L, double* out, void* workspace, size_t workspace_bytes,
                          void* stream)
 {
@@ -908,7 +942,7 @@ int rmb_symmetric_finish(int wall, int flags, long n, long target_offset, long n
   if (n_targets == 0) return 0;
   if (!acc || !out) return fail(RMB_E_ARG, "null device pointer");
   Call c;
-  const int rc = sym_call(c, wall, flags, n, nullptr, nullptr, eta, a, L, workspace, workspace_bytes, stream);
+  const int rc = sym_call(c, block, wall, flags, n, nullptr, nullptr, eta, a, L, workspace, workspace_bytes, stream);
   if (rc != 0) return rc;
   c.tgt_off = target_offset; c.n_tgt = n_targets; c.out = out;
   return sym_finish(c, acc);

@@ -144,10 +144,11 @@ def _length3(periodic_length):
 
 
 def symmetric_partial(r_vectors, force, eta, a, rank=0, world=1, acc=None, flags=0, wall=SINGLE_WALL,
-                      periodic_length=None):
+                      periodic_length=None, block=UF):
     """Multi-rank pair-symmetric UF product, step 1 (rmb_symmetric_partial): this rank's share of the unordered
-    pairs, raw sums for ALL blobs -> acc (device tensor, summed over the ranks by the caller).  wall = SINGLE_WALL
-    or NO_WALL; periodic_length may be periodic in x and/or y only."""
+    pairs, raw sums for ALL blobs -> acc (device tensor, summed over the ranks by the caller).  block = UF with
+    wall = SINGLE_WALL or NO_WALL, or UT / WF / WT with SINGLE_WALL; periodic_length may be periodic in x and/or y
+    only."""
     lib = _lib.load()
     dev = _device(r_vectors.device if isinstance(r_vectors, torch.Tensor) else None)
     n = (r_vectors.numel() if isinstance(r_vectors, torch.Tensor) else np.asarray(r_vectors).size) // 3
@@ -157,16 +158,17 @@ def symmetric_partial(r_vectors, force, eta, a, rank=0, world=1, acc=None, flags
         Lc = _length3(periodic_length)
         if acc is None:
             acc = torch.empty(lib.rmb_symmetric_acc_len(n), dtype=torch.float64, device=dev)
-        ws = _workspace(lib.rmb_workspace_bytes(UF, FP64, n, n, Lc), dev)
-        _lib.check(lib.rmb_symmetric_partial(wall, flags | default_flags, n, rank, world, r.data_ptr(), f.data_ptr(),
+        ws = _workspace(lib.rmb_workspace_bytes(block, FP64, n, n, Lc), dev)
+        _lib.check(lib.rmb_symmetric_partial(block, wall, flags | default_flags, n, rank, world, r.data_ptr(), f.data_ptr(),
                                              float(eta), float(a), Lc, acc.data_ptr(), ws.data_ptr(), ws.numel(),
                                              torch.cuda.current_stream(dev).cuda_stream))
     return acc
 
 
-def symmetric_finish(n, acc, eta, a, targets=None, out=None, flags=0, wall=SINGLE_WALL, periodic_length=None):
+def symmetric_finish(n, acc, eta, a, targets=None, out=None, flags=0, wall=SINGLE_WALL, periodic_length=None,
+                     block=UF):
     """Step 2 (rmb_symmetric_finish) after the ranks' acc have been summed: self term, normalisation, damping for
-    the target range.  Must follow symmetric_partial (same wall, a, periodic_length) on the same device: it reads
+    the target range.  Must follow symmetric_partial (same block, wall, a, periodic_length) on the same device: it reads
     that call's workspace."""
     lib = _lib.load()
     dev = acc.device
@@ -175,8 +177,8 @@ def symmetric_finish(n, acc, eta, a, targets=None, out=None, flags=0, wall=SINGL
         if out is None:
             out = torch.empty(3 * cnt, dtype=torch.float64, device=dev)
         Lc = _length3(periodic_length)
-        ws = _workspace(lib.rmb_workspace_bytes(UF, FP64, n, n, Lc), dev)
-        _lib.check(lib.rmb_symmetric_finish(wall, flags | default_flags, n, off, cnt, acc.data_ptr(), float(eta),
+        ws = _workspace(lib.rmb_workspace_bytes(block, FP64, n, n, Lc), dev)
+        _lib.check(lib.rmb_symmetric_finish(block, wall, flags | default_flags, n, off, cnt, acc.data_ptr(), float(eta),
                                             float(a), Lc, out.data_ptr(), ws.data_ptr(), ws.numel(),
                                             torch.cuda.current_stream(dev).cuda_stream))
     return out

@@ -85,13 +85,15 @@ class ShardedMobility:
             self.block, self.wall, r, v, self.eta, self.a, periodic_length=self.L, precision=self.precision,
             targets=targets))
 
-        # Pair-symmetric schedule (UF, fp64, wall or no wall, not periodic in z): the unordered pairs are dealt to the
+        # Pair-symmetric schedule (UF wall / no wall, UT / WF / WT wall; fp64, not periodic in z): the unordered pairs are dealt to the
         # ranks row group by row group, every rank accumulates raw sums for ALL blobs, the sums are all-reduced
         # (the one extra data-path collective: 24 N bytes) and each rank finishes its own target range.
         open_z = periodic_length is None or not bool(np.asarray(
             periodic_length.cpu() if isinstance(periodic_length, torch.Tensor) else periodic_length).reshape(-1)[2] > 0)
-        self.symmetric = (symmetric is not False and local_product is None and block == _mb.UF and
-                          wall in (_mb.SINGLE_WALL, _mb.NO_WALL) and precision == _mb.FP64 and open_z and
+        eligible = ((block == _mb.UF and wall in (_mb.SINGLE_WALL, _mb.NO_WALL)) or
+                    (block in (_mb.UT, _mb.WF, _mb.WT) and wall == _mb.SINGLE_WALL))
+        self.symmetric = (symmetric is not False and local_product is None and eligible and
+                          precision == _mb.FP64 and open_z and
                           (symmetric is True or n >= 16384))
         self._acc = None
 
@@ -101,11 +103,11 @@ class ShardedMobility:
             return self._product(self.r, full, (self.offset, self.count))
         n = self.r.numel() // 3
         self._acc = _mb.symmetric_partial(self.r, full, self.eta, self.a, rank=self.rank, world=self.world,
-                                          acc=self._acc, wall=self.wall, periodic_length=self.L)
+                                          acc=self._acc, wall=self.wall, periodic_length=self.L, block=self.block)
         if self.world > 1:
             dist.all_reduce(self._acc, group=self.group)
         return _mb.symmetric_finish(n, self._acc, self.eta, self.a, targets=(self.offset, self.count),
-                                    wall=self.wall, periodic_length=self.L)
+                                    wall=self.wall, periodic_length=self.L, block=self.block)
 
 
 def _global_norm(x, group):

@@ -197,7 +197,7 @@ extern "C" void host_uf_sym(int wall, long n, const double* r, const double* f, 
 
 // ---- the same with pseudo-periodic images in x / y: per unordered pair the wrap once, then every box with (r, -r);
 // ---- box b seen from i is box -b seen from j, so the loop over b covers all boxes of both directions ----
-extern "C" void host_uf_sym_periodic(int wall, long n, const double* r, const double* f, double eta, double a,
+extern "C" void host_sym_periodic(int block, int wall, long n, const double* r, const double* f, double eta, double a,
                                      const double* L, double* out)
 {
   typedef double T;
@@ -233,21 +233,38 @@ extern "C" void host_uf_sym_periodic(int wall, long n, const double* r, const do
         if (i == j && b == box.central) continue;
         const T bx = rx + box.s[b][0], by = ry + box.s[b][1];
         const T r2 = bx * bx + by * by + rz * rz;
+        const bool nr = lt4(r2);
+        T* ui = &u[3 * i];
+        T* uj = &u[3 * j];
+        const T *vi = rec[i].v, *vj = rec[j].v;
         if (i == j) {     // own image: one direction (the opposite one is box -b of the same loop)
-          if (wall) pair_uf_wall_sym<T, false>(bx, by, rz, hi + hj, hi, hj, C.ht2, C.ht4, C, rec[i].v, rec[j].v, lt4(r2), r2, &u[3 * i], &u[3 * i]);
-          else pair_uf_free_sym<T, false>(bx, by, rz, C, rec[i].v, rec[j].v, lt4(r2), r2, &u[3 * i], &u[3 * i]);
+          if (block == UF && wall) pair_uf_wall_sym<T, false>(bx, by, rz, hi + hj, hi, hj, C.ht2, C.ht4, C, vi, vj, nr, r2, ui, ui);
+          else if (block == UF) pair_uf_free_sym<T, false>(bx, by, rz, C, vi, vj, nr, r2, ui, ui);
+          else if (block == WF) pair_wf_wall_sym<T, false>(bx, by, rz, hi + hj, hi, hj, C.ht4, C, vi, vj, nr, r2, ui, ui);
+          else if (block == UT) pair_ut_wall_sym<T, false>(bx, by, rz, hi + hj, hi, hj, C.ht4, C, vi, vj, nr, r2, ui, ui);
+          else pair_wt_wall_sym<T, false>(bx, by, rz, hi + hj, C.ht4, hj, C, vi, vj, nr, r2, ui, ui);
         } else {
-          if (wall) pair_uf_wall_sym<T, true>(bx, by, rz, hi + hj, hi, hj, C.ht2, C.ht4, C, rec[i].v, rec[j].v, lt4(r2), r2, &u[3 * i], &u[3 * j]);
-          else pair_uf_free_sym<T, true>(bx, by, rz, C, rec[i].v, rec[j].v, lt4(r2), r2, &u[3 * i], &u[3 * j]);
+          if (block == UF && wall) pair_uf_wall_sym<T, true>(bx, by, rz, hi + hj, hi, hj, C.ht2, C.ht4, C, vi, vj, nr, r2, ui, uj);
+          else if (block == UF) pair_uf_free_sym<T, true>(bx, by, rz, C, vi, vj, nr, r2, ui, uj);
+          else if (block == WF) pair_wf_wall_sym<T, true>(bx, by, rz, hi + hj, hi, hj, C.ht4, C, vi, vj, nr, r2, ui, uj);
+          else if (block == UT) pair_ut_wall_sym<T, true>(bx, by, rz, hi + hj, hi, hj, C.ht4, C, vi, vj, nr, r2, ui, uj);
+          else pair_wt_wall_sym<T, true>(bx, by, rz, hi + hj, C.ht4, hj, C, vi, vj, nr, r2, ui, uj);
         }
       }
     }
   }
-  const double norm = block_norm(UF, eta, a);
+  const double norm = block_norm(block, eta, a);
   for (long i = 0; i < n; i++) {
     T ux = u[3 * i], uy = u[3 * i + 1], uz = u[3 * i + 2];
-    if (wall) self_apply<T, UF, true>(rec[i].z * inva, rec[i].v, ux, uy, uz);
-    else self_apply<T, UF, false>(rec[i].z * inva, rec[i].v, ux, uy, uz);
+    const T h = rec[i].z * inva;
+    switch (block * 2 + (wall ? 1 : 0)) {
+      case UF * 2 + 1: self_apply<T, UF, true>(h, rec[i].v, ux, uy, uz); break;
+      case UF * 2: self_apply<T, UF, false>(h, rec[i].v, ux, uy, uz); break;
+      case UT * 2 + 1: self_apply<T, UT, true>(h, rec[i].v, ux, uy, uz); break;
+      case WF * 2 + 1: self_apply<T, WF, true>(h, rec[i].v, ux, uy, uz); break;
+      case WT * 2 + 1: self_apply<T, WT, true>(h, rec[i].v, ux, uy, uz); break;
+      default: break;
+    }
     out[3 * i] = ux * norm * damp[i]; out[3 * i + 1] = uy * norm * damp[i]; out[3 * i + 2] = uz * norm * damp[i];
   }
 }

@@ -354,8 +354,8 @@ def test_symmetric_periodic_large_default_and_multi_rank(mb):
     assert lib.rmb_launches_per_product(mb.UF, mb.SINGLE_WALL, mb.FP64, 0, n, n, Lc) == 3
     Lz = (ctypes.c_double * 3)(side, 0.0, side)
     # periodic z: row kernel whatever the flags (its launch count depends on the source split only)
-    assert (lib.rmb_launches_per_product(mb.UF, mb.SINGLE_WALL, mb.FP64, mb.SYMMETRIC, 10 ** 6, 10 ** 6, Lz) ==
-            lib.rmb_launches_per_product(mb.UF, mb.SINGLE_WALL, mb.FP64, mb.DETERMINISTIC, 10 ** 6, 10 ** 6, Lz) == 2)
+    assert lib.rmb_launches_per_product(mb.UF, mb.SINGLE_WALL, mb.FP64, mb.SYMMETRIC, 10 ** 7, 10 ** 7, Lz) == 2
+    assert lib.rmb_launches_per_product(mb.UF, mb.SINGLE_WALL, mb.FP64, mb.SYMMETRIC, 10 ** 7, 10 ** 7, Lc) == 3
     r = torch.from_numpy(side * rng.random((n, 3))).cuda()
     f = torch.from_numpy(rng.standard_normal((n, 3))).cuda()
     for w in (mb.SINGLE_WALL, mb.NO_WALL):
@@ -373,3 +373,65 @@ def test_symmetric_periodic_large_default_and_multi_rank(mb):
                                   targets=(5000, 5032))
     sym = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, periodic_length=L)
     assert relerr(sym[3 * 5000:3 * 5032].cpu().numpy(), ref) < TOL64
+
+
+# ---- pair-symmetric kernel for the rotation blocks (UT / WF / WT, single wall) ----
+@pytest.mark.parametrize("blk", ["UT", "WF", "WT"])
+@pytest.mark.parametrize("lname", ["open", "xy", "x", "xyz"])
+@pytest.mark.parametrize("cloud", ["dense", "dilute"])
+def test_symmetric_rotation_blocks_golden(mb, golden, cloud, lname, blk):
+    r, v = golden[f"{cloud}/r"], golden[f"{cloud}/v"]
+    a, eta = golden[f"{cloud}/a_eta"]
+    L = golden[f"{cloud}/L_{lname}"]
+    out = mb.mobility_product(BLOCK_ID[blk], mb.SINGLE_WALL, r, v, eta, a, periodic_length=L, flags=mb.SYMMETRIC)
+    assert relerr(out, golden[f"{cloud}/{lname}/single_wall/{blk}"]) < TOL64
+    if blk == "UT" and f"{cloud}/{lname}/in_plane/UT" in golden:
+        out = mb.mobility_product(BLOCK_ID[blk], mb.SINGLE_WALL, r, v, eta, a, periodic_length=L,
+                                  flags=mb.SYMMETRIC | mb.IN_PLANE)
+        assert relerr(out, golden[f"{cloud}/{lname}/in_plane/UT"]) < TOL64
+
+
+@pytest.mark.parametrize("n", [1, 2, 33, 255, 257, 1000, 3001])
+def test_symmetric_rotation_blocks_ragged_vs_oracle(mb, n):
+    import oracle
+    rng = np.random.default_rng(n + 17)
+    a, eta = 0.21, 1.3
+    side = (2.0 + 0.3 * n ** (1 / 3)) * a
+    r = side * rng.random((n, 3))                                  # dense: overlaps and blobs below z = a
+    v = rng.standard_normal((n, 3))
+    for L in (None, np.array([side, 1.2 * side, 0.0])):
+        if L is not None and n > 1000:
+            continue
+        for blk in ("UT", "WF", "WT"):
+            ref = oracle.mobility_product(blk, "single_wall", r, v, eta, a, periodic_length=L)
+            out = mb.mobility_product(BLOCK_ID[blk], mb.SINGLE_WALL, r, v, eta, a, periodic_length=L, flags=mb.SYMMETRIC)
+            assert relerr(out, ref) < TOL64, (blk, L)
+
+
+@pytest.mark.parametrize("blk", ["UT", "WF", "WT"])
+def test_symmetric_rotation_blocks_large_default_and_multi_rank(mb, blk):
+    """n >= RMB_SYMMETRIC_MIN_N: default = symmetric kernel, equal to the row kernel (RMB_DETERMINISTIC) and to the
+    multi-rank form (world = 3 on one device, sums added by hand); no-wall rotation blocks keep the row kernel"""
+    from rigidmultiblobswall_b200 import _lib
+    lib = _lib.load()
+    rng = np.random.default_rng(41)
+    n, a, eta = 20000, 0.13, 7.0
+    b = BLOCK_ID[blk]
+    assert lib.rmb_launches_per_product(b, mb.SINGLE_WALL, mb.FP64, 0, 10 ** 7, 10 ** 7, None) == 3
+    assert lib.rmb_launches_per_product(b, mb.NO_WALL, mb.FP64, mb.SYMMETRIC, 10 ** 7, 10 ** 7, None) == 2
+    side = (n * 4 * np.pi / 3 / 0.1) ** (1 / 3) * a
+    r = torch.from_numpy(side * rng.random((n, 3))).cuda()
+    v = torch.from_numpy(rng.standard_normal((n, 3))).cuda()
+    for L in (None, np.array([side, side, 0.0])):
+        det = mb.mobility_product(b, mb.SINGLE_WALL, r, v, eta, a, periodic_length=L, flags=mb.DETERMINISTIC)
+        sym = mb.mobility_product(b, mb.SINGLE_WALL, r, v, eta, a, periodic_length=L)
+        assert float(torch.linalg.norm(sym - det) / torch.linalg.norm(det)) < 1e-13
+        world = 3
+        acc = sum(mb.symmetric_partial(r, v, eta, a, rank=k, world=world, block=b, periodic_length=L).clone()
+                  for k in range(world))
+        out = torch.cat([mb.symmetric_finish(n, acc, eta, a, targets=t, block=b, periodic_length=L)
+                         for t in ((0, 9000), (9000, 11000))])
+        assert float(torch.linalg.norm(out - det) / torch.linalg.norm(det)) < 1e-13
+    nw = mb.mobility_product(b, mb.NO_WALL, r, v, eta, a, flags=mb.SYMMETRIC)
+    nw_det = mb.mobility_product(b, mb.NO_WALL, r, v, eta, a, flags=mb.DETERMINISTIC)
+    assert torch.equal(nw, nw_det)

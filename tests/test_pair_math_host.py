@@ -42,13 +42,14 @@ def harness(tmp_path_factory):
         lib.host_uf_sym(int(wall), r.shape[0], r.ctypes.data_as(dp), f.ctypes.data_as(dp), eta, a, out.ctypes.data_as(dp))
         return out
 
-    lib.host_uf_sym_periodic.argtypes = [ctypes.c_int, ctypes.c_long, dp, dp, ctypes.c_double, ctypes.c_double, dp, dp]
+    lib.host_sym_periodic.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_long, dp, dp, ctypes.c_double,
+                                      ctypes.c_double, dp, dp]
 
-    def run_sym_periodic(r, f, eta, a, L, wall=True):
+    def run_sym_periodic(r, f, eta, a, L, wall=True, block="UF"):
         r, f, L = (np.ascontiguousarray(x, dtype=np.float64) for x in (r, f, L))
         out = np.empty(r.size)
-        lib.host_uf_sym_periodic(int(wall), r.shape[0], r.ctypes.data_as(dp), f.ctypes.data_as(dp), eta, a,
-                                 L.ctypes.data_as(dp), out.ctypes.data_as(dp))
+        lib.host_sym_periodic(BLOCKS[block], int(wall), r.shape[0], r.ctypes.data_as(dp), f.ctypes.data_as(dp), eta, a,
+                              L.ctypes.data_as(dp), out.ctypes.data_as(dp))
         return out
 
     def run(block, wall, r, va, eta, a, L, fp32=False, in_plane=False, vb=None):
@@ -170,3 +171,15 @@ def test_pair_symmetric_periodic_outside_cell(harness):
     for wall, name in ((True, "single_wall"), (False, "no_wall")):
         ref = oracle.mobility_product("UF", name, r, f, eta, a, periodic_length=L)
         assert relerr(harness.sym_periodic(r, f, eta, a, L, wall=wall), ref) < 1e-12
+
+
+@pytest.mark.parametrize("block", ["UT", "WF", "WT"])
+@pytest.mark.parametrize("lname", ["open", "xy", "x"])
+@pytest.mark.parametrize("cloud", ["dense", "dilute"])
+def test_pair_symmetric_rotation_blocks(golden, harness, cloud, lname, block):
+    """pair_{ut,wf,wt}_wall_sym: the (j <- i) interaction from the (i <- j) one's shared factors, r -> -r and the
+    wall term's height exchanged; open and pseudo-periodic"""
+    r, v = golden[f"{cloud}/r"], golden[f"{cloud}/v"]
+    a, eta = golden[f"{cloud}/a_eta"]
+    L = golden[f"{cloud}/L_{lname}"]
+    assert relerr(harness.sym_periodic(r, v, eta, a, L, block=block), golden[f"{cloud}/{lname}/single_wall/{block}"]) < 1e-12

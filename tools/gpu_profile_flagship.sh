@@ -9,5 +9,5 @@ echo "== bench"; timeout 900 python bench.py > gpurun_out/${T}_bench_1gpu.json 2
 echo "== ref"; timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${T}_ref.json 2> gpurun_out/${T}_ref.err; echo "rc=$?"
 CMD="python bench.py --n 200000 --steps 2 --warmup 1 --no-cpu --no-parity"
 echo "== launch list"; ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches.csv $CMD > gpurun_out/${T}_ncu_launch.log 2>&1; echo "rc=$?"
-echo "== full"; ncu --set full --clock-control none --import-source on -k regex:uf_sym_kernel -s 1 -c 1 -o gpurun_out/${T}_sym_full -f $CMD > gpurun_out/${T}_ncu_full.log 2>&1; echo "rc=$?"
-echo "== traffic"; timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:uf_sym_kernel -c 2 --csv --log-file gpurun_out/${T}_traffic_n1m.csv python bench.py --steps 1 --warmup 1 --no-cpu --no-parity --no-solve > gpurun_out/${T}_traffic.log 2>&1; echo "rc=$?"; tail -3 gpurun_out/${T}_traffic_n1m.csv
+echo "== full"; ncu --set full --clock-control none --import-source on -k regex:sym_kernel -s 1 -c 1 -o gpurun_out/${T}_sym_full -f $CMD > gpurun_out/${T}_ncu_full.log 2>&1; echo "rc=$?"
+echo "== traffic"; timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:sym_kernel -c 2 --csv --log-file gpurun_out/${T}_traffic_n1m.csv python bench.py --steps 1 --warmup 1 --no-cpu --no-parity --no-solve > gpurun_out/${T}_traffic.log 2>&1; echo "rc=$?"; tail -3 gpurun_out/${T}_traffic_n1m.csv
