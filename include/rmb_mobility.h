@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define RMB_VERSION 103 /* 0.1.1 */
+#define RMB_VERSION 104 /* 0.1.1 */
 
 /* block: which mobility block is applied (mobility.py naming in comments) */
 #define RMB_UF 0    /* *_mobility_trans_times_force        (mobility.py:222,288,1119,1132) */
@@ -112,7 +112,8 @@ int rmb_mobility_product(int block, int wall, int precision, int flags,
 
 /*
  * Multi-rank form of the pair-symmetric product (fp64; block = RMB_UF with wall = RMB_SINGLE_WALL or RMB_NO_WALL,
- * or block = RMB_UT / RMB_WF / RMB_WT with RMB_SINGLE_WALL; all n blobs targets and sources; L = NULL or
+ * or block = RMB_UT / RMB_WF / RMB_WT / RMB_UF_UT with RMB_SINGLE_WALL (vec_b = torque for RMB_UF_UT, else NULL);
+ * all n blobs targets and sources; L = NULL or
  * pseudo-periodic in x and/or y only: L[2] must be 0).  Every rank calls
  *   rmb_symmetric_partial()  raw pair sums, for ALL blobs, of this rank's share of the unordered pairs (row groups
  *                            rank, rank + world, ... of the triangular schedule) -> acc, overwritten;
@@ -126,7 +127,7 @@ int rmb_mobility_product(int block, int wall, int precision, int flags,
  */
 size_t rmb_symmetric_acc_len(long n);
 int rmb_symmetric_partial(int block, int wall, int flags, long n, int rank, int world, const double *r,
-                          const double *vec, double eta, double a, const double *L, double *acc, void *workspace,
+                          const double *vec_a, const double *vec_b, double eta, double a, const double *L, double *acc, void *workspace,
                           size_t workspace_bytes, void *stream);
 int rmb_symmetric_finish(int block, int wall, int flags, long n, long target_offset, long n_targets, const double *acc,
                          double eta, double a, const double *L, double *out, void *workspace,

@@ -53,7 +53,7 @@ def load():
     lib.rmb_symmetric_acc_len.argtypes = [ctypes.c_long]
     lib.rmb_symmetric_partial.restype = ctypes.c_int
     lib.rmb_symmetric_partial.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_long, ctypes.c_int, ctypes.c_int, c_dp,
-                                          c_dp, ctypes.c_double, ctypes.c_double, ctypes.POINTER(ctypes.c_double),
+                                          c_dp, c_dp, ctypes.c_double, ctypes.c_double, ctypes.POINTER(ctypes.c_double),
                                           c_dp, c_dp, ctypes.c_size_t, c_dp]
     lib.rmb_symmetric_finish.restype = ctypes.c_int
     lib.rmb_symmetric_finish.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_long, ctypes.c_long, ctypes.c_long, c_dp,

@@ -330,7 +330,7 @@ __global__ void finish_kernel(const MfArgs<T, (BLOCK == UF_UT) ? 2 : 1> A)
 // self term, the normalisation and the damping.  Padding records (zero force) are handled by the TAIL
 // instantiations: a pair with a padding blob is given a finite dummy geometry.
 struct SymArgs {
-  const SrcRec<double, 1>* src;   // n_tiles * TILE records; padding = zero force (geometry overridden, see TAIL)
+  const double* src;              // n_tiles * TILE records of W words {x, y, z, v[3 NV], pad}; padding = zero vectors (see TAIL)
   double* acc;                    // [n_tiles * TILE][3], zeroed before the launch
   long n;                         // real blobs; records [n, n_tiles * TILE) are zero-force padding
   int n_tiles, n_split;
@@ -343,9 +343,15 @@ struct SymArgs {
 };
 
 // Registers of one lane: NT blobs, one from each of the warp's NT consecutive blocks.
-template <int NT>
+template <int NT, int NV = 1>
 struct SymLane {
-  double x[NT], y[NT], h[NT], h2[NT], h4[NT], f[NT][3], u[NT][3];
+  double x[NT], y[NT], h[NT], h2[NT], h4[NT], f[NT][3 * NV], u[NT][3];
+};
+
+// vectors per blob and record words of a block (UF_UT: force and torque / a)
+template <int BLOCK> struct SymRec {
+  static constexpr int NV = (BLOCK == UF_UT) ? 2 : 1;
+  static constexpr int W = RecWords<double, NV>::value;
 };
 
 // One block J against the lane's blobs k in [K0, K0 + NK): 32 rotation steps, both directions, then the
@@ -365,6 +371,9 @@ __device__ __forceinline__ void sym_pair(double rx, double ry, double rz, double
   if (BLOCK == UF) {
     if (WALL) pair_uf_wall_sym<T, BOTH>(rx, ry, rz, Rz, hi, hj, hi2, hi4, C, vi, vj, any_near, r2, ui, uj);
     else pair_uf_free_sym<T, BOTH>(rx, ry, rz, C, vi, vj, any_near, r2, ui, uj);
+  } else if (BLOCK == UF_UT) {   // u = UF f + UT (t / a): the two share the geometry and both rsqrt (common subexpressions)
+    pair_uf_wall_sym<T, BOTH>(rx, ry, rz, Rz, hi, hj, hi2, hi4, C, vi, vj, any_near, r2, ui, uj);
+    pair_ut_wall_sym<T, BOTH>(rx, ry, rz, Rz, hi, hj, hi4, C, vi + 3, vj + 3, any_near, r2, ui, uj);
   } else if (BLOCK == WF) {
     pair_wf_wall_sym<T, BOTH>(rx, ry, rz, Rz, hi, hj, hi4, C, vi, vj, any_near, r2, ui, uj);
   } else if (BLOCK == UT) {
@@ -391,11 +400,12 @@ __device__ __forceinline__ void sym_geometry(const SymArgs& A, double xi, double
 }
 
 template <int BLOCK, int NT, int K0, int NK, bool TAIL, bool WALL, bool PER>
-__device__ __forceinline__ void sym_block(const double* __restrict__ blk, int lane, SymLane<NT>& L, const SymArgs& A,
+__device__ __forceinline__ void sym_block(const double* __restrict__ blk, int lane,
+                                          SymLane<NT, SymRec<BLOCK>::NV>& L, const SymArgs& A,
                                           double* __restrict__ acc_j, long i0, long j0)
 {
   typedef double T;
-  constexpr int W = 6;
+  constexpr int W = SymRec<BLOCK>::W;
   const UfCtx<T>& C = A.K;
   const long n = A.n;
   T aj[3] = {0, 0, 0};
@@ -441,11 +451,11 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
 // Diagonal block (J == the block of blob k): ordered pairs (l, (l + s) & 31), s = 1..31, one direction.
 // PER: also s = 0, the blob's own images in the non-central boxes.
 template <int BLOCK, int NT, bool TAIL, bool WALL, bool PER>
-__device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lane, SymLane<NT>& L, int k,
+__device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lane, SymLane<NT, SymRec<BLOCK>::NV>& L, int k,
                                          const SymArgs& A, long i0)
 {
   typedef double T;
-  constexpr int W = 6;
+  constexpr int W = SymRec<BLOCK>::W;
   const UfCtx<T>& C = A.K;
   const long n = A.n;
 #pragma unroll 2
@@ -481,7 +491,7 @@ template <int BLOCK, bool TMA, int NT, bool WALL, bool PER>
 __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) sym_kernel(const __grid_constant__ SymArgs A)
 {
   typedef double T;
-  constexpr int W = 6;
+  constexpr int W = SymRec<BLOCK>::W;
   constexpr uint32_t TILE_BYTES = TILE * W * sizeof(T);
   constexpr int ROW = TPB * NT;                            // blobs of one row group (CTA)
   __shared__ alignas(128) T tile[TMA ? STAGES : 1][TILE * W];
@@ -491,19 +501,22 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) sym_kernel(const __grid_con
   const int g = A.row_first + blockIdx.x * A.row_stride;   // row group of ROW blobs
   const long I0 = ((long)g * (TPB / 32) + warp) * NT;      // this warp's first block of 32
 
-  SymLane<NT> L;
+  constexpr int NV = SymRec<BLOCK>::NV;
+  const T* srcw = A.src;
+  SymLane<NT, NV> L;
 #pragma unroll
   for (int k = 0; k < NT; k++) {
-    const SrcRec<T, 1>& me = A.src[(I0 + k) * 32 + lane];
-    L.x[k] = me.x; L.y[k] = me.y; L.h[k] = PER ? me.z * A.inva : me.z;
+    const T* me = srcw + ((I0 + k) * 32 + lane) * W;
+    L.x[k] = me[0]; L.y[k] = me[1]; L.h[k] = PER ? me[2] * A.inva : me[2];
     L.h2[k] = 2.0 * L.h[k]; L.h4[k] = 4.0 * L.h[k];
 #pragma unroll
-    for (int c = 0; c < 3; c++) { L.f[k][c] = me.v[c]; L.u[k][c] = 0.0; }
+    for (int c = 0; c < 3 * NV; c++) L.f[k][c] = me[3 + c];
+#pragma unroll
+    for (int c = 0; c < 3; c++) L.u[k][c] = 0.0;
   }
   // this CTA's part of the row's tiles [g * ROW / TILE, n_tiles)
   const SymRowPart part = sym_row_part(g, ROW, TILE, A.n_tiles, (int)blockIdx.y, A.n_split);
   const int v0 = part.v0, v1 = part.v1;
-  const T* srcw = reinterpret_cast<const T*>(A.src);
 
   if (TMA) {
     if (tid == 0) {
@@ -564,15 +577,16 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB) sym_kernel(const __grid_con
 
 // out = B (acc + self term) / (8 pi eta a) for the targets [tgt_off, tgt_off + n_tgt)
 template <int BLOCK, bool WALL>
-__global__ void sym_finish_kernel(const SrcRec<double, 1>* __restrict__ src, const double* __restrict__ acc,
+__global__ void sym_finish_kernel(const SrcRec<double, SymRec<BLOCK>::NV>* __restrict__ src, const double* __restrict__ acc,
                                   const double* __restrict__ damp, long tgt_off, long n_tgt, double norm, int in_plane,
                                   double zscale, double* __restrict__ out)
 {
   const long li = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (li >= n_tgt) return;
   const long gi = tgt_off + li;
-  const SrcRec<double, 1>& me = src[gi];
-  double sv[3] = {me.v[0], me.v[1], me.v[2]};
+  const SrcRec<double, SymRec<BLOCK>::NV>& me = src[gi];
+  double sv[6] = {me.v[0], me.v[1], me.v[2], 0.0, 0.0, 0.0};
+  if (SymRec<BLOCK>::NV == 2) { sv[3] = me.v[3]; sv[4] = me.v[4]; sv[5] = me.v[5]; }
   double dx = acc[3 * gi], dy = acc[3 * gi + 1], dz = acc[3 * gi + 2];
   self_apply<double, BLOCK, WALL>(me.z * zscale, sv, dx, dy, dz);   // zscale: 1/a when the records are unscaled
   const double sc = norm * damp[gi];
@@ -632,10 +646,10 @@ int make_plan(int block, int precision, long n_tgt, long n_src, const double* L,
   p.off_damp = align_up(p.rec_bytes, 256);
   p.off_partial = align_up(p.off_damp + (size_t)n_src * sizeof(double), 256);
   p.total = p.off_partial + (p.n_split > 1 ? (size_t)p.n_split * n_tgt * 3 * word : 0);
-  // accumulators of the pair-symmetric kernel (fp64 single-wall UF over all blobs)
+  // accumulators of the pair-symmetric kernel (fp64, every blob a target; see use_symmetric)
   p.off_acc = align_up(p.total, 256);
   p.sym_split = 1;
-  if (block == RMB_UF && precision == RMB_FP64 && n_tgt == n_src) {
+  if (block >= RMB_UF && block <= RMB_UF_UT && precision == RMB_FP64 && n_tgt == n_src) {
     p.total = p.off_acc + (size_t)p.n_tiles * TILE * 3 * sizeof(double);
     const int rows = p.n_tiles * (TILE / (TPB * RMB_SYM_NT));
     int ss = (RMB_WAVES * sms * 3 + rows - 1) / (rows > 0 ? rows : 1);
@@ -645,13 +659,13 @@ int make_plan(int block, int precision, long n_tgt, long n_src, const double* L,
   return 0;
 }
 
-// The pair-symmetric kernel exists for UF (wall or no wall) and UT / WF / WT (wall), fp64, every blob a target, open
+// The pair-symmetric kernel exists for UF (wall or no wall) and UT / WF / WT / fused UF+UT (wall), fp64, every blob a target, open
 // or pseudo-periodic in x/y (a periodic z breaks |R|^2 = r^2 + 4 h_i h_j).  Forced by RMB_SYMMETRIC, chosen by default from
 // RMB_SYMMETRIC_MIN_N blobs on (below that the row kernel is as fast), never with RMB_DETERMINISTIC.
 bool use_symmetric(int block, int wall, int precision, int flags, long n_tgt, long n_src, const double* L)
 {
   const bool blk = (block == RMB_UF && (wall == RMB_SINGLE_WALL || wall == RMB_NO_WALL)) ||
-                   ((block == RMB_UT || block == RMB_WF || block == RMB_WT) && wall == RMB_SINGLE_WALL);
+                   ((block == RMB_UT || block == RMB_WF || block == RMB_WT || block == RMB_UF_UT) && wall == RMB_SINGLE_WALL);
   const bool ok = blk && precision == RMB_FP64 &&
                   !(L && L[2] > 0) && n_tgt == n_src && TILE % (TPB * RMB_SYM_NT) == 0;
   const bool want = (flags & RMB_SYMMETRIC) || (!(flags & RMB_DETERMINISTIC) && n_src >= RMB_SYMMETRIC_MIN_N);
@@ -716,18 +730,22 @@ int launch(const Call& c)
 int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
 {
   const Plan& p = c.plan;
-  SrcRec<double, 1>* rec = reinterpret_cast<SrcRec<double, 1>*>(c.ws);
   double* damp = reinterpret_cast<double*>(c.ws + p.off_damp);
   const long n_pad = (long)p.n_tiles * TILE;
   const int in_plane = (c.flags & RMB_IN_PLANE) ? 1 : 0;
   const bool wall = c.wall == RMB_SINGLE_WALL;
   const bool per = c.L[0] > 0 || c.L[1] > 0;
-  prepare_kernel<double, 1><<<(unsigned)((n_pad + 255) / 256), 256, 0, c.stream>>>(
-      c.n_src, n_pad, c.r, c.va, c.vb, c.a, wall ? 1 : 0, per ? 0 : 1, in_plane, rec, damp);
+  const unsigned prep_blocks = (unsigned)((n_pad + 255) / 256);
+  if (c.block == RMB_UF_UT)
+    prepare_kernel<double, 2><<<prep_blocks, 256, 0, c.stream>>>(c.n_src, n_pad, c.r, c.va, c.vb, c.a, wall ? 1 : 0, per ? 0 : 1,
+                                                                 in_plane, reinterpret_cast<SrcRec<double, 2>*>(c.ws), damp);
+  else
+    prepare_kernel<double, 1><<<prep_blocks, 256, 0, c.stream>>>(c.n_src, n_pad, c.r, c.va, c.vb, c.a, wall ? 1 : 0, per ? 0 : 1,
+                                                                 in_plane, reinterpret_cast<SrcRec<double, 1>*>(c.ws), damp);
   cudaError_t e = cudaMemsetAsync(acc, 0, (size_t)n_pad * 3 * sizeof(double), c.stream);
   if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: memset");
   SymArgs A;
-  A.src = rec; A.acc = acc; A.n = c.n_src; A.n_tiles = p.n_tiles; A.n_split = p.sym_split;
+  A.src = reinterpret_cast<const double*>(c.ws); A.acc = acc; A.n = c.n_src; A.n_tiles = p.n_tiles; A.n_split = p.sym_split;
   A.row_first = row_first; A.row_stride = row_stride;
   A.K = make_uf_ctx<double>(0.0);
   A.P.nbox = p.n_boxes;
@@ -747,7 +765,10 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
     A.n_split = split;
     const dim3 grid((unsigned)rows, (unsigned)split);
     constexpr int NT = RMB_SYM_NT;
-    if (c.block == RMB_UT) {
+    if (c.block == RMB_UF_UT) {
+      if (per) sym_kernel<UF_UT, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
+      else sym_kernel<UF_UT, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
+    } else if (c.block == RMB_UT) {
       if (per) sym_kernel<UT, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
       else sym_kernel<UT, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
     } else if (c.block == RMB_WF) {
@@ -771,14 +792,15 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
 int sym_finish(const Call& c, const double* acc)
 {
   const Plan& p = c.plan;
-  const SrcRec<double, 1>* rec = reinterpret_cast<const SrcRec<double, 1>*>(c.ws);
   const double* damp = reinterpret_cast<const double*>(c.ws + p.off_damp);
   const unsigned nb = (unsigned)((c.n_tgt + 127) / 128);
   const int in_plane = (c.flags & RMB_IN_PLANE) ? 1 : 0;
   const double zscale = (c.L[0] > 0 || c.L[1] > 0) ? 1.0 / c.a : 1.0;
   const double norm = block_norm(c.block, c.eta, c.a);
-#define RMB_SYM_FINISH(B, W) sym_finish_kernel<B, W><<<nb, 128, 0, c.stream>>>(rec, acc, damp, c.tgt_off, c.n_tgt, norm, in_plane, zscale, c.out)
-  if (c.block == RMB_UT) RMB_SYM_FINISH(UT, true);
+#define RMB_SYM_FINISH(B, W) sym_finish_kernel<B, W><<<nb, 128, 0, c.stream>>>( \
+      reinterpret_cast<const SrcRec<double, SymRec<B>::NV>*>(c.ws), acc, damp, c.tgt_off, c.n_tgt, norm, in_plane, zscale, c.out)
+  if (c.block == RMB_UF_UT) RMB_SYM_FINISH(UF_UT, true);
+  else if (c.block == RMB_UT) RMB_SYM_FINISH(UT, true);
   else if (c.block == RMB_WF) RMB_SYM_FINISH(WF, true);
   else if (c.block == RMB_WT) RMB_SYM_FINISH(WT, true);
   else if (c.wall == RMB_SINGLE_WALL) RMB_SYM_FINISH(UF, true);
@@ -900,11 +922,12 @@ size_t rmb_symmetric_acc_len(long n)
   return n <= 0 ? 0 : (size_t)((n + TILE - 1) / TILE) * TILE * 3;
 }
 
-static int sym_call(Call& c, int block, int wall, int flags, long n, const double* r, const double* force, double eta, double a,
+static int sym_call(Call& c, int block, int wall, int flags, long n, const double* r, const double* force,
+                    const double* vec_b, double eta, double a,
                     const double* L, void* workspace, size_t workspace_bytes, void* stream)
 {
   if (n <= 0) return fail(RMB_E_ARG, "n must be positive");
-  if (block < RMB_UF || block > RMB_WT) return fail(RMB_E_ARG, "block must be RMB_UF, RMB_UT, RMB_WF or RMB_WT");
+  if (block < RMB_UF || block > RMB_UF_UT) return fail(RMB_E_ARG, "block must be RMB_UF..RMB_UF_UT");
   if (wall != RMB_SINGLE_WALL && !(wall == RMB_NO_WALL && block == RMB_UF))
     return fail(RMB_E_ARG, "the pair-symmetric product exists for RMB_SINGLE_WALL (all blocks) and RMB_NO_WALL (RMB_UF)");
   if (L && L[2] > 0) return fail(RMB_E_ARG, "the pair-symmetric product cannot be periodic in z");
@@ -913,7 +936,7 @@ static int sym_call(Call& c, int block, int wall, int flags, long n, const doubl
   if ((reinterpret_cast<uintptr_t>(workspace) & 15) != 0) return fail(RMB_E_ARG, "workspace must be 16-byte aligned");
   c.block = block; c.wall = wall; c.precision = RMB_FP64; c.flags = flags;
   c.n_tgt = n; c.n_src = n; c.tgt_off = 0;
-  c.r = r; c.va = force; c.vb = nullptr; c.eta = eta; c.a = a;
+  c.r = r; c.va = force; c.vb = vec_b; c.eta = eta; c.a = a;
   for (int d = 0; d < 3; d++) c.L[d] = L ? L[d] : 0.0;
   c.out = nullptr; c.ws = static_cast<char*>(workspace); c.stream = static_cast<cudaStream_t>(stream);
   const int rc = make_plan(block, RMB_FP64, n, n, c.L, c.plan);
@@ -922,14 +945,15 @@ static int sym_call(Call& c, int block, int wall, int flags, long n, const doubl
   return 0;
 }
 
-int rmb_symmetric_partial(int block, int wall, int flags, long n, int rank, int world, const double* r, const double* force,
-                          double eta, double a, const double* L, double* acc, void* workspace, size_t workspace_bytes,
+int rmb_symmetric_partial(int block, int wall, int flags, long n, int rank, int world, const double* r,
+                          const double* force, const double* vec_b, double eta, double a, const double* L, double* acc, void* workspace, size_t workspace_bytes,
                           void* stream)
 {
   if (world < 1 || rank < 0 || rank >= world) return fail(RMB_E_ARG, "0 <= rank < world required");
   if (!r || !force || !acc) return fail(RMB_E_ARG, "null device pointer");
+  if (block == RMB_UF_UT && !vec_b) return fail(RMB_E_ARG, "RMB_UF_UT needs vec_b (torque)");
   Call c;
-  const int rc = sym_call(c, block, wall, flags, n, r, force, eta, a, L, workspace, workspace_bytes, stream);
+  const int rc = sym_call(c, block, wall, flags, n, r, force, vec_b, eta, a, L, workspace, workspace_bytes, stream);
   return rc != 0 ? rc : sym_partial(c, acc, rank, world);
 }
 
@@ -942,7 +966,7 @@ int rmb_symmetric_finish(int block, int wall, int flags, long n, long target_off
   if (n_targets == 0) return 0;
   if (!acc || !out) return fail(RMB_E_ARG, "null device pointer");
   Call c;
-  const int rc = sym_call(c, block, wall, flags, n, nullptr, nullptr, eta, a, L, workspace, workspace_bytes, stream);
+  const int rc = sym_call(c, block, wall, flags, n, nullptr, nullptr, nullptr, eta, a, L, workspace, workspace_bytes, stream);
   if (rc != 0) return rc;
   c.tgt_off = target_offset; c.n_tgt = n_targets; c.out = out;
   return sym_finish(c, acc);

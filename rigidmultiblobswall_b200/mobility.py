@@ -144,22 +144,24 @@ def _length3(periodic_length):
 
 
 def symmetric_partial(r_vectors, force, eta, a, rank=0, world=1, acc=None, flags=0, wall=SINGLE_WALL,
-                      periodic_length=None, block=UF):
+                      periodic_length=None, block=UF, vec_b=None):
     """Multi-rank pair-symmetric UF product, step 1 (rmb_symmetric_partial): this rank's share of the unordered
     pairs, raw sums for ALL blobs -> acc (device tensor, summed over the ranks by the caller).  block = UF with
-    wall = SINGLE_WALL or NO_WALL, or UT / WF / WT with SINGLE_WALL; periodic_length may be periodic in x and/or y
-    only."""
+    wall = SINGLE_WALL or NO_WALL, or UT / WF / WT / UF_UT (vec_b = torque) with SINGLE_WALL; periodic_length may be
+    periodic in x and/or y only."""
     lib = _lib.load()
     dev = _device(r_vectors.device if isinstance(r_vectors, torch.Tensor) else None)
     n = (r_vectors.numel() if isinstance(r_vectors, torch.Tensor) else np.asarray(r_vectors).size) // 3
     with torch.cuda.device(dev):
         r = _as_device_f64(r_vectors, 3 * n, dev)
         f = _as_device_f64(force, 3 * n, dev)
+        vb = _as_device_f64(vec_b, 3 * n, dev) if block == UF_UT else None
         Lc = _length3(periodic_length)
         if acc is None:
             acc = torch.empty(lib.rmb_symmetric_acc_len(n), dtype=torch.float64, device=dev)
         ws = _workspace(lib.rmb_workspace_bytes(block, FP64, n, n, Lc), dev)
         _lib.check(lib.rmb_symmetric_partial(block, wall, flags | default_flags, n, rank, world, r.data_ptr(), f.data_ptr(),
+                                             vb.data_ptr() if vb is not None else None,
                                              float(eta), float(a), Lc, acc.data_ptr(), ws.data_ptr(), ws.numel(),
                                              torch.cuda.current_stream(dev).cuda_stream))
     return acc

@@ -435,3 +435,54 @@ def test_symmetric_rotation_blocks_large_default_and_multi_rank(mb, blk):
     nw = mb.mobility_product(b, mb.NO_WALL, r, v, eta, a, flags=mb.SYMMETRIC)
     nw_det = mb.mobility_product(b, mb.NO_WALL, r, v, eta, a, flags=mb.DETERMINISTIC)
     assert torch.equal(nw, nw_det)
+
+
+# ---- pair-symmetric kernel for the fused product u = UF f + UT t (single wall) ----
+@pytest.mark.parametrize("lname", ["open", "xy", "x", "xyz"])
+@pytest.mark.parametrize("cloud", ["dense", "dilute"])
+def test_symmetric_fused_force_torque_golden(mb, golden, cloud, lname):
+    r, f = golden[f"{cloud}/r"], golden[f"{cloud}/v"]
+    a, eta = golden[f"{cloud}/a_eta"]
+    L = golden[f"{cloud}/L_{lname}"]
+    t = f[::-1].copy()
+    import oracle
+    ref = golden[f"{cloud}/{lname}/single_wall/UF"] + oracle.mobility_product("UT", "single_wall", r, t, eta, a, L)
+    out = mb.mobility_product(mb.UF_UT, mb.SINGLE_WALL, r, f, eta, a, periodic_length=L, vec_b=t, flags=mb.SYMMETRIC)
+    assert relerr(out, ref) < TOL64
+
+
+@pytest.mark.parametrize("n", [1, 33, 257, 1000, 3001])
+def test_symmetric_fused_ragged_vs_oracle(mb, n):
+    import oracle
+    rng = np.random.default_rng(n + 23)
+    a, eta = 0.21, 1.3
+    side = (2.0 + 0.3 * n ** (1 / 3)) * a
+    r = side * rng.random((n, 3))
+    f, t = rng.standard_normal((n, 3)), rng.standard_normal((n, 3))
+    for L in (None, np.array([side, 0.0, 0.0])):
+        ref = (oracle.mobility_product("UF", "single_wall", r, f, eta, a, periodic_length=L) +
+               oracle.mobility_product("UT", "single_wall", r, t, eta, a, periodic_length=L))
+        out = mb.mobility_product(mb.UF_UT, mb.SINGLE_WALL, r, f, eta, a, periodic_length=L, vec_b=t, flags=mb.SYMMETRIC)
+        assert relerr(out, ref) < TOL64
+
+
+def test_symmetric_fused_large_default_and_multi_rank(mb):
+    rng = np.random.default_rng(43)
+    n, a, eta = 20000, 0.13, 7.0
+    side = (n * 4 * np.pi / 3 / 0.1) ** (1 / 3) * a
+    r = torch.from_numpy(side * rng.random((n, 3))).cuda()
+    f = torch.from_numpy(rng.standard_normal((n, 3))).cuda()
+    t = torch.from_numpy(rng.standard_normal((n, 3))).cuda()
+    for L in (None, np.array([side, side, 0.0])):
+        det = mb.mobility_product(mb.UF_UT, mb.SINGLE_WALL, r, f, eta, a, periodic_length=L, vec_b=t, flags=mb.DETERMINISTIC)
+        two = (mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, periodic_length=L, flags=mb.DETERMINISTIC) +
+               mb.mobility_product(mb.UT, mb.SINGLE_WALL, r, t, eta, a, periodic_length=L, flags=mb.DETERMINISTIC))
+        assert float(torch.linalg.norm(two - det) / torch.linalg.norm(det)) < 1e-13
+        sym = mb.single_wall_mobility_trans_times_force_torque_b200(r, f, t, eta, a, periodic_length=L)   # default
+        assert float(torch.linalg.norm(sym - det) / torch.linalg.norm(det)) < 1e-13
+        world = 3
+        acc = sum(mb.symmetric_partial(r, f, eta, a, rank=k, world=world, block=mb.UF_UT, vec_b=t,
+                                       periodic_length=L).clone() for k in range(world))
+        out = torch.cat([mb.symmetric_finish(n, acc, eta, a, targets=tg, block=mb.UF_UT, periodic_length=L)
+                         for tg in ((0, 9000), (9000, 11000))])
+        assert float(torch.linalg.norm(out - det) / torch.linalg.norm(det)) < 1e-13
