@@ -488,7 +488,7 @@ __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lan
 }
 
 template <int BLOCK, bool TMA, int NT, bool WALL, bool PER>
-__global__ void __launch_bounds__(TPB, RMB_SYM_MINB) sym_kernel(const __grid_constant__ SymArgs A)
+__global__ void __launch_bounds__(TPB, (PER && BLOCK == UF && WALL) ? 4 : RMB_SYM_MINB) sym_kernel(const __grid_constant__ SymArgs A)
 {
   typedef double T;
   constexpr int W = SymRec<BLOCK>::W;

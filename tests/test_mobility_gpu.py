@@ -486,3 +486,35 @@ def test_symmetric_fused_large_default_and_multi_rank(mb):
         out = torch.cat([mb.symmetric_finish(n, acc, eta, a, targets=tg, block=mb.UF_UT, periodic_length=L)
                          for tg in ((0, 9000), (9000, 11000))])
         assert float(torch.linalg.norm(out - det) / torch.linalg.norm(det)) < 1e-13
+
+
+@pytest.mark.parametrize("flags", [4, 8])
+@pytest.mark.parametrize("blk", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("periodic", [False, True])
+def test_workspace_is_exactly_what_rmb_workspace_bytes_says(mb, blk, periodic, flags):
+    """C ABI called with a workspace of exactly rmb_workspace_bytes() followed by a guard region: the product
+    (pair-symmetric, flags = 4, and row kernel, flags = 8) must leave the guard untouched"""
+    from rigidmultiblobswall_b200 import _lib
+    lib = _lib.load()
+    rng = np.random.default_rng(5)
+    n, a, eta = 3000, 0.2, 1.0
+    r = torch.from_numpy(8.0 * rng.random((n, 3))).cuda()
+    va = torch.from_numpy(rng.standard_normal((n, 3))).cuda()
+    vb = torch.from_numpy(rng.standard_normal((n, 3))).cuda()
+    Lc = (ctypes.c_double * 3)(8.0, 8.0, 0.0) if periodic else None
+    nbytes = lib.rmb_workspace_bytes(blk, mb.FP64, n, n, Lc)
+    guard = 1 << 16
+    ws = torch.full((nbytes + guard,), 0xAB, dtype=torch.uint8, device="cuda")
+    out = torch.empty(3 * n, dtype=torch.float64, device="cuda")
+    rc = lib.rmb_mobility_product(blk, mb.SINGLE_WALL, mb.FP64, flags, n, n, 0, r.data_ptr(), va.data_ptr(),
+                                  vb.data_ptr(), eta, a, Lc, out.data_ptr(), ws.data_ptr(), nbytes,
+                                  torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, lib.rmb_last_error()
+    torch.cuda.synchronize()
+    assert bool((ws[nbytes:] == 0xAB).all())
+    assert bool(torch.isfinite(out).all())
+    # one byte less is refused
+    rc = lib.rmb_mobility_product(blk, mb.SINGLE_WALL, mb.FP64, flags, n, n, 0, r.data_ptr(), va.data_ptr(),
+                                  vb.data_ptr(), eta, a, Lc, out.data_ptr(), ws.data_ptr(), nbytes - 1,
+                                  torch.cuda.current_stream().cuda_stream)
+    assert rc != 0

@@ -37,4 +37,28 @@ def launches(path):
     for k, (n, t) in sorted(agg.items(), key=lambda x: -x[1][1])[:25]:
         print("%-72s %6d %14.0f %6.2f%%" % (k, n, t, 100 * t / tot))
 
-{"full": full, "list": launches}[sys.argv[1]](sys.argv[2])
+def kernels(path, pairs=None):
+    """per-kernel table from an `ncu --metrics sm__pipe_fp64_cycles_active...,smsp__inst_executed.sum,
+    gpu__time_duration.sum,launch__registers_per_thread --csv` log; pairs = pair-boxes per launch (for instr/pair)"""
+    txt = open(path).read()
+    txt = txt[txt.index('"ID"'):]
+    rows = collections.OrderedDict()
+    for row in csv.DictReader(io.StringIO(txt)):
+        key = (row["ID"], row["Kernel Name"])
+        rows.setdefault(key, {})[row["Metric Name"]] = (float(row["Metric Value"].replace(",", "")), row["Metric Unit"])
+    for (_, name), m in rows.items():
+        if "sym_kernel" not in name and "mf_kernel" not in name and "st_kernel" not in name:
+            continue
+        ms, unit = m["gpu__time_duration.sum"]
+        ms *= {"ns": 1e-6, "nsecond": 1e-6, "us": 1e-3, "usecond": 1e-3, "ms": 1.0, "msecond": 1.0, "s": 1e3, "second": 1e3}[unit]
+        pipe = [v for k, (v, _) in m.items() if k.startswith("sm__pipe_fp64_cycles_active")][0]
+        inst = m["smsp__inst_executed.sum"][0]
+        line = "%-62s fp64_pipe_active %5.1f%%  regs %3d  ms %8.1f" % (name[:62], pipe, m["launch__registers_per_thread"][0], ms)
+        if pairs:
+            line += "  warp instr per 32 interactions %6.1f" % (inst * 32 / float(pairs))
+        print(line)
+
+if sys.argv[1] == "kernels":
+    kernels(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else None)
+else:
+    {"full": full, "list": launches}[sys.argv[1]](sys.argv[2])

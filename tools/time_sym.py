@@ -6,6 +6,7 @@ import numpy as np, torch
 from rigidmultiblobswall_b200 import mobility as mb
 from bench import make_cloud
 res = {}
+only = os.environ.get("TIME_SYM_ONLY")          # e.g. "xy_UF_wall,open_UF_wall"
 for n in [int(x) for x in sys.argv[1:]] or [400000]:
     r, f, a, eta = make_cloud(n)
     side = float(r[:, :2].max())
@@ -14,6 +15,8 @@ for n in [int(x) for x in sys.argv[1:]] or [400000]:
         for wname, wall, block in (("UF_wall", mb.SINGLE_WALL, mb.UF), ("UF_nowall", mb.NO_WALL, mb.UF),
                                    ("UT_wall", mb.SINGLE_WALL, mb.UT), ("WF_wall", mb.SINGLE_WALL, mb.WF),
                                    ("WT_wall", mb.SINGLE_WALL, mb.WT)):
+            if only and "%s_%s" % (bname, wname) not in only.split(","):
+                continue
             outs = {}
             for name, fl in (("row", mb.DETERMINISTIC), ("symmetric", mb.SYMMETRIC)):
                 reps = 3 if boxes * n <= 400000 else 1
