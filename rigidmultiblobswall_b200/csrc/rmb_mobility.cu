@@ -53,8 +53,11 @@ namespace {
 #define RMB_SYM_NT 1      // blobs per lane of the pair-symmetric kernel (1 or 2; TILE must be a multiple of 128 NT).
                           // Measured at N = 400k: 334.6 (1) vs 336.8 (2) G pairs/s, and 270 vs 252 at N = 20k
 #endif
+// Resident CTAs per SM the pair-symmetric kernels are compiled for (register cap 65536 / (128 * n)).  Measured
+// (tools/tune.sh, N = 400k): UF 4 -> 5 CTAs +1.5 % (open), +2.5 % (9 boxes; uncapped 134 registers = 3 CTAs: -7 %);
+// WF, WT +0.5..3 %; UT -1.7 %; the fused block is fastest uncapped (142 / 155 registers).
 #ifndef RMB_SYM_MINB
-#define RMB_SYM_MINB 1
+#define RMB_SYM_MINB(BLOCK) (((BLOCK) == UF || (BLOCK) == WF || (BLOCK) == WT) ? 5 : 1)
 #endif
 #ifndef RMB_WAVES
 #define RMB_WAVES 10
@@ -488,7 +491,7 @@ __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lan
 }
 
 template <int BLOCK, bool TMA, int NT, bool WALL, bool PER>
-__global__ void __launch_bounds__(TPB, (PER && BLOCK == UF && WALL) ? 4 : RMB_SYM_MINB) sym_kernel(const __grid_constant__ SymArgs A)
+__global__ void __launch_bounds__(TPB, RMB_SYM_MINB(BLOCK)) sym_kernel(const __grid_constant__ SymArgs A)
 {
   typedef double T;
   constexpr int W = SymRec<BLOCK>::W;
