@@ -59,6 +59,15 @@ namespace {
 #ifndef RMB_SYM_MINB
 #define RMB_SYM_MINB(BLOCK) (((BLOCK) == UF || (BLOCK) == WF || (BLOCK) == WT) ? 5 : 1)
 #endif
+// A launch of the pair-symmetric kernel (a rank's share of the triangular rows) is split over blockIdx.y until it
+// has RMB_SYM_WAVES waves of RMB_SYM_RESIDENT CTAs per SM.  Measured (tools/time_rank_share.py, tools/tune.sh):
+// 10 -> 24 waves: one rank's eighth of N = 1M 383.5 -> 375.1 ms (ideal 369.4), N = 100k +4 %, N = 50k +6 %.
+#ifndef RMB_SYM_RESIDENT
+#define RMB_SYM_RESIDENT 5
+#endif
+#ifndef RMB_SYM_WAVES
+#define RMB_SYM_WAVES 24
+#endif
 #ifndef RMB_WAVES
 #define RMB_WAVES 10
 #endif
@@ -617,7 +626,6 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 struct Plan {
   int n_tiles, n_boxes, n_vt, n_split, vt_per_split, tgt_blocks;
   size_t rec_bytes, off_damp, off_partial, off_acc, total;
-  int sym_split;   // blockIdx.y extent of sym_kernel
 };
 
 // One place decides the decomposition; rmb_workspace_bytes and the launch
@@ -651,14 +659,8 @@ int make_plan(int block, int precision, long n_tgt, long n_src, const double* L,
   p.total = p.off_partial + (p.n_split > 1 ? (size_t)p.n_split * n_tgt * 3 * word : 0);
   // accumulators of the pair-symmetric kernel (fp64, every blob a target; see use_symmetric)
   p.off_acc = align_up(p.total, 256);
-  p.sym_split = 1;
-  if (block >= RMB_UF && block <= RMB_UF_UT && precision == RMB_FP64 && n_tgt == n_src) {
+  if (block >= RMB_UF && block <= RMB_UF_UT && precision == RMB_FP64 && n_tgt == n_src)
     p.total = p.off_acc + (size_t)p.n_tiles * TILE * 3 * sizeof(double);
-    const int rows = p.n_tiles * (TILE / (TPB * RMB_SYM_NT));
-    int ss = (RMB_WAVES * sms * 3 + rows - 1) / (rows > 0 ? rows : 1);
-    if (ss > p.n_tiles / 4) ss = p.n_tiles / 4;
-    p.sym_split = ss < 1 ? 1 : ss;
-  }
   return 0;
 }
 
@@ -748,7 +750,7 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
   cudaError_t e = cudaMemsetAsync(acc, 0, (size_t)n_pad * 3 * sizeof(double), c.stream);
   if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: memset");
   SymArgs A;
-  A.src = reinterpret_cast<const double*>(c.ws); A.acc = acc; A.n = c.n_src; A.n_tiles = p.n_tiles; A.n_split = p.sym_split;
+  A.src = reinterpret_cast<const double*>(c.ws); A.acc = acc; A.n = c.n_src; A.n_tiles = p.n_tiles; A.n_split = 1;
   A.row_first = row_first; A.row_stride = row_stride;
   A.K = make_uf_ctx<double>(0.0);
   A.P.nbox = p.n_boxes;
@@ -763,8 +765,8 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
   const long rows = (rows_all - row_first + row_stride - 1) / row_stride;
   if (rows > 0) {
     // rows are triangular (1 .. n_tiles tiles): split them over blockIdx.y until THIS launch (a rank's share of
-    // the rows) has at least RMB_WAVES waves of resident CTAs, so that the tail is short
-    const int split = sym_split_for(rows, (long)sm_count() * 4, RMB_WAVES, p.n_tiles);
+    // the rows) has at least RMB_SYM_WAVES waves of resident CTAs, so that the tail is short
+    const int split = sym_split_for(rows, (long)sm_count() * RMB_SYM_RESIDENT, RMB_SYM_WAVES, p.n_tiles);
     A.n_split = split;
     const dim3 grid((unsigned)rows, (unsigned)split);
     constexpr int NT = RMB_SYM_NT;
