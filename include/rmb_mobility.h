@@ -56,10 +56,12 @@ extern "C" {
 /* flags */
 #define RMB_IN_PLANE 1    /* in_plane_* (mobility.py:255,454,1166,1235): z column and row zero */
 #define RMB_NO_TMA 2      /* stage source tiles with plain loads instead of cp.async.bulk (debug) */
-#define RMB_SYMMETRIC 4   /* RMB_UF (single wall or no wall), fp64, open boundaries, n_targets == n_sources: evaluate every
-                             unordered pair once and update both blobs (sums accumulated with atomics: results
-                             agree with the row kernel to rounding, but are not bit-reproducible run to run).
-                             Without this flag the symmetric kernel is still chosen for eligible calls with
+#define RMB_SYMMETRIC 4   /* evaluate every unordered pair once and update both blobs.  Exists for fp64, n_targets ==
+                             n_sources, L[2] <= 0 (open or pseudo-periodic in x / y), and RMB_UF (single wall or no
+                             wall) or RMB_UT / RMB_WF / RMB_WT / RMB_UF_UT (single wall); any other call ignores the
+                             flag and takes the row kernel.  Sums are accumulated with atomics: results agree with
+                             the row kernel to rounding, but are not bit-reproducible run to run.  Without this
+                             flag the symmetric kernel is still chosen for eligible calls with
                              n_sources >= RMB_SYMMETRIC_MIN_N */
 #define RMB_DETERMINISTIC 8 /* never use the pair-symmetric kernel: one thread per target, fixed summation order */
 #define RMB_SYMMETRIC_MIN_N 16384
