@@ -9,6 +9,9 @@ iteration as interpreted loops over bodies:
     K_matrix_T_vector_prod            multi_bodies.py:350-371
     linear_operator_rigid             multi_bodies.py:424-471  (no constraints, no prescribed kinematics)
     build_block_diagonal_preconditioner  multi_bodies.py:752-903 (free bodies)
+    solve_mobility_problem / solve_resistance_problem / body_mobility
+                                      the `mobility`, `resistance` and `body_mobility` schemes of
+                                      multi_bodies_utilities.py:449-540, :549-574, :576-600
     get_blobs_r_vectors               multi_bodies.py:196-208 / body.py:64-80
 
 The `bodies` argument is a RigidBodies object (the device-resident form of
@@ -219,6 +222,10 @@ class BlockDiagonalPreconditioner:
         """y = P^-1 w = Lc w (maps the preconditioned Lanczos noise back, stochastic_forcing.py:256)."""
         return self._unpad((self.chol @ self._pad(w.reshape(-1)).unsqueeze(2)).squeeze(2))
 
+    def M_inv_mult(self, w):
+        """y = blockdiag(M_b^-1) w: the blob-level preconditioner of the resistance problem M lambda = rhs."""
+        return self._unpad((self.M_inv @ self._pad(w.reshape(-1)).unsqueeze(2)).squeeze(2))
+
 
 def build_block_diagonal_preconditioners_det_stoch(bodies, r_vectors, Nblobs, eta, a, *args, **kwargs):
     """multi_bodies.build_block_diagonal_preconditioners_det_stoch (multi_bodies.py:480): returns
@@ -267,3 +274,58 @@ def solve_mobility_problem(bodies, force_torque, eta, a, tolerance=1e-8, periodi
     if float(nrm) > 0:
         x = x * nrm
     return x[n3:].reshape(-1, 6), x[:n3].reshape(-1, 3), its, info
+
+
+def solve_resistance_problem(bodies, velocity, eta, a, tolerance=1e-8, periodic_length=None, slip=None,
+                             PC=None, restart=60, maxiter=1000, callback=None, mobility_vector_prod=None, wall=True):
+    """The `resistance` scheme of multi_bodies_utilities.py:549-574 on the device, matrix-free:
+    blob forces lambda from  M lambda = slip + K velocity,  body force-torques = K^T lambda.
+    The reference forms the dense blob mobility and calls LAPACK (O(N^3)); here M is applied by the pair kernel
+    inside GMRES(60), right-preconditioned with the bodies' own M_b^-1 (the blocks the mobility problem's
+    preconditioner already holds), RHS scaled to unit norm as in the mobility scheme.
+    velocity: (U_b, omega_b) per body, any shape with 6*Nbodies entries.
+    Returns (force [Nbodies, 6], lambda_blobs [Nblobs, 3], iterations, info)."""
+    from . import solvers
+    dev = bodies.device
+    r = bodies.get_r_vectors()
+    U = torch.as_tensor(velocity, dtype=torch.float64).to(dev).reshape(-1)
+    rhs = K_matrix_vector_prod(bodies, U, r_vectors=r).reshape(-1)
+    if slip is not None:
+        rhs = rhs + torch.as_tensor(slip, dtype=torch.float64).to(dev).reshape(-1)
+    nrm = torch.linalg.norm(rhs)
+    if float(nrm) > 0:
+        rhs = rhs / nrm
+    if PC is None:
+        PC = BlockDiagonalPreconditioner(bodies, r, eta, a, wall=wall)
+    if mobility_vector_prod is None:
+        mobility_vector_prod = (mobility.single_wall_mobility_trans_times_force_b200 if wall
+                                else mobility.no_wall_mobility_trans_times_force_b200)
+    A = lambda v: mobility_vector_prod(r, v, eta, a, periodic_length=periodic_length)
+    lam, info, its = solvers.gmres(A, rhs, tol=tolerance, restart=restart, maxiter=maxiter, M=PC.M_inv_mult,
+                                   callback=callback)
+    if float(nrm) > 0:
+        lam = lam * nrm
+    force = K_matrix_T_vector_prod(bodies, lam, r_vectors=r).reshape(-1, 6)
+    return force, lam.reshape(-1, 3), its, info
+
+
+def body_mobility(bodies, eta, a, tolerance=1e-10, periodic_length=None, PC=None, mobility_vector_prod=None, wall=True):
+    """The `body_mobility` scheme of multi_bodies_utilities.py:576-600: the dense (6 Nbodies)^2 grand mobility
+    N = (K^T M^-1 K)^-1 of the suspension.  The reference inverts the dense blob mobility; here column c is the
+    velocity answer of the mobility problem for the unit force-torque e_c (6 Nbodies preconditioned GMRES solves
+    sharing one preconditioner), so it is meant for the small suspensions that scheme is used on.
+    Returns N as a [6 Nbodies, 6 Nbodies] device tensor (row/column order: body-major, (U, omega) / (F, T))."""
+    n6 = 6 * bodies.n_bodies
+    if PC is None:
+        PC = BlockDiagonalPreconditioner(bodies, bodies.get_r_vectors(), eta, a, wall=wall)
+    N = torch.empty(n6, n6, dtype=torch.float64, device=bodies.device)
+    e = torch.zeros(n6, dtype=torch.float64, device=bodies.device)
+    for c in range(n6):
+        e.zero_()
+        e[c] = 1.0
+        vel, _, _, info = solve_mobility_problem(bodies, e, eta, a, tolerance=tolerance, periodic_length=periodic_length,
+                                                 PC=PC, mobility_vector_prod=mobility_vector_prod, wall=wall)
+        if info != 0:
+            raise RuntimeError("body_mobility: GMRES did not converge for column %d" % c)
+        N[:, c] = vel.reshape(-1)
+    return N

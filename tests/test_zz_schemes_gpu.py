@@ -1,0 +1,73 @@
+"""GPU parity tests of the `resistance` and `body_mobility` schemes (multi_bodies_utilities.py:549-600) against
+golden outputs of the reference's own dense computation (tests/golden/resistance_golden.npz, generator
+tests/golden/make_golden_resistance.py).  The product path is matrix-free (pair kernel inside GMRES); the reference
+inverts the dense blob mobility, so the two answers are independent."""
+import os
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def relerr(x, ref):
+    x = x.detach().cpu().numpy() if hasattr(x, "detach") else np.asarray(x)
+    return np.linalg.norm(x.reshape(-1) - np.asarray(ref).reshape(-1)) / np.linalg.norm(ref)
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return (np.load(os.path.join(HERE, "golden", "rigid_golden.npz")),
+            np.load(os.path.join(HERE, "golden", "resistance_golden.npz")))
+
+
+@pytest.fixture(scope="module")
+def setup(gold):
+    from rigidmultiblobswall_b200 import rigid
+    rg, _ = gold
+    bodies = rigid.RigidBodies(rg["struct/boomerang_N_15"], rg["rigid/location"], rg["rigid/quaternion"])
+    a, eta, _ = rg["rigid/a_eta_tol"]
+    PC = rigid.BlockDiagonalPreconditioner(bodies, bodies.get_r_vectors(), eta, a)
+    return rigid, bodies, PC, float(eta), float(a)
+
+
+@pytest.mark.parametrize("key", ["noslip", "slip"])
+def test_resistance_problem(gold, setup, key):
+    _, g = gold
+    rigid, bodies, PC, eta, a = setup
+    slip = g["slip"] if key == "slip" else None
+    force, lam, its, info = rigid.solve_resistance_problem(bodies, g["velocity"], eta, a, tolerance=1e-10, slip=slip,
+                                                           PC=PC)
+    assert info == 0 and 0 < its <= 60
+    assert tuple(force.shape) == (12, 6) and tuple(lam.shape) == (180, 3)
+    # GMRES stops at relative residual 1e-10, cond(M) = 73 (stored in the golden file)
+    assert relerr(lam, g[f"resistance/{key}/force_blobs"]) < 1e-8
+    assert relerr(force, g[f"resistance/{key}/force"]) < 1e-8
+
+
+def test_resistance_problem_builds_its_own_preconditioner(gold, setup):
+    _, g = gold
+    rigid, bodies, _, eta, a = setup
+    force, _, _, info = rigid.solve_resistance_problem(bodies, torch.from_numpy(g["velocity"]).cuda(), eta, a,
+                                                       tolerance=1e-9)
+    assert info == 0
+    assert relerr(force, g["resistance/noslip/force"]) < 1e-7
+
+
+def test_blob_preconditioner_is_the_block_inverse(setup):
+    rigid, bodies, PC, eta, a = setup
+    w = torch.randn(3 * bodies.n_blobs, dtype=torch.float64, device="cuda",
+                    generator=torch.Generator(device="cuda").manual_seed(5))
+    y = PC.M_inv_mult(w).reshape(12, 45, 1)
+    assert relerr((PC.M_blobs @ y).reshape(-1), w.cpu().numpy()) < 1e-11
+
+
+def test_body_mobility(gold, setup):
+    _, g = gold
+    rigid, bodies, PC, eta, a = setup
+    N = rigid.body_mobility(bodies, eta, a, tolerance=1e-10, PC=PC)
+    assert tuple(N.shape) == (72, 72)
+    assert relerr(N, g["body_mobility/N"]) < 1e-8
+    assert relerr(N, N.T.cpu().numpy()) < 1e-8
