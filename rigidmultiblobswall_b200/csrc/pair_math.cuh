@@ -601,4 +601,53 @@ RMB_HD void pair_wt_wall_sym(T rx, T ry, T rz, T Rz, T hi4, T hj, const UfCtx<T>
   if (BOTH) wt_direction<T>(-rx, -ry, -rz, Rz, Aa, Bc, q5a, q5b, ti, wj);
 }
 
+// Free-space twins (no_wall UT / WF / WT).  The coupling kf (v x r) is the same function for UT and WF; with
+// w = kf r formed once, the two directions are u_i += v_j x w and u_j -= v_i x w: 3 + 6 + 6 FP64 instructions
+// after the shared kf (row kernel: 9 per interaction plus its own kf).
+template <typename T, bool BOTH>
+RMB_HD void pair_coupling_free_sym(T rx, T ry, T rz, const UfCtx<T>& C, const T* vi, const T* vj, bool any_near, T r2,
+                                   T* ui, T* uj)
+{
+  const T kf = coupling_k(r2, any_near, C);
+  const T wx = kf * rx, wy = kf * ry, wz = kf * rz;
+  ui[0] = RMB_FMA(vj[1], wz, ui[0]); ui[0] = RMB_FMA(-vj[2], wy, ui[0]);
+  ui[1] = RMB_FMA(vj[2], wx, ui[1]); ui[1] = RMB_FMA(-vj[0], wz, ui[1]);
+  ui[2] = RMB_FMA(vj[0], wy, ui[2]); ui[2] = RMB_FMA(-vj[1], wx, ui[2]);
+  if (BOTH) {
+    uj[0] = RMB_FMA(vi[2], wy, uj[0]); uj[0] = RMB_FMA(-vi[1], wz, uj[0]);
+    uj[1] = RMB_FMA(vi[0], wz, uj[1]); uj[1] = RMB_FMA(-vi[2], wx, uj[1]);
+    uj[2] = RMB_FMA(vi[1], wx, uj[2]); uj[2] = RMB_FMA(-vi[0], wy, uj[2]);
+  }
+}
+
+// Free-space WT is even in r: w += A tau + Bc (r . tau) r in both directions with the same A, Bc.
+template <typename T, bool BOTH>
+RMB_HD void pair_wt_free_sym(T rx, T ry, T rz, const UfCtx<T>& C, const T* ti, const T* tj, bool any_near, T r2, T* wi,
+                             T* wj)
+{
+  const T invr = rsqrt_full(r2, C.c38, C.khalf);
+  const T invr2 = invr * invr;
+  const T invr3 = invr2 * invr;
+  T A = T(-0.5) * invr3;
+  T Bc = (T(1.5) * invr2) * invr3;
+  if (any_near) {
+    const T r = r2 * invr;
+    const T An = RMB_FMA(RMB_FMA(T(0.078125), r2, T(-0.84375)), r, T(1.0));
+    const T Bn = RMB_FMA(T(-0.046875), r, T(0.28125) * invr);
+    const bool near = lt4(r2);
+    A = near ? An : A;
+    Bc = near ? Bn : Bc;
+  }
+  {
+    const T B = Bc * RMB_FMA(rz, tj[2], RMB_FMA(ry, tj[1], rx * tj[0]));
+    wi[0] = RMB_FMA(A, tj[0], wi[0]); wi[1] = RMB_FMA(A, tj[1], wi[1]); wi[2] = RMB_FMA(A, tj[2], wi[2]);
+    wi[0] = RMB_FMA(B, rx, wi[0]); wi[1] = RMB_FMA(B, ry, wi[1]); wi[2] = RMB_FMA(B, rz, wi[2]);
+  }
+  if (BOTH) {
+    const T B = Bc * RMB_FMA(rz, ti[2], RMB_FMA(ry, ti[1], rx * ti[0]));
+    wj[0] = RMB_FMA(A, ti[0], wj[0]); wj[1] = RMB_FMA(A, ti[1], wj[1]); wj[2] = RMB_FMA(A, ti[2], wj[2]);
+    wj[0] = RMB_FMA(B, rx, wj[0]); wj[1] = RMB_FMA(B, ry, wj[1]); wj[2] = RMB_FMA(B, rz, wj[2]);
+  }
+}
+
 }  // namespace rmb

@@ -383,6 +383,15 @@ __device__ __forceinline__ void sym_pair(double rx, double ry, double rz, double
   if (BLOCK == UF) {
     if (WALL) pair_uf_wall_sym<T, BOTH>(rx, ry, rz, Rz, hi, hj, hi2, hi4, C, vi, vj, any_near, r2, ui, uj);
     else pair_uf_free_sym<T, BOTH>(rx, ry, rz, C, vi, vj, any_near, r2, ui, uj);
+  } else if (!WALL) {            // free space: UT and WF are the same function kf (v x r); fused = UF + that
+    if (BLOCK == UF_UT) {
+      pair_uf_free_sym<T, BOTH>(rx, ry, rz, C, vi, vj, any_near, r2, ui, uj);
+      pair_coupling_free_sym<T, BOTH>(rx, ry, rz, C, vi + 3, vj + 3, any_near, r2, ui, uj);
+    } else if (BLOCK == WT) {
+      pair_wt_free_sym<T, BOTH>(rx, ry, rz, C, vi, vj, any_near, r2, ui, uj);
+    } else {
+      pair_coupling_free_sym<T, BOTH>(rx, ry, rz, C, vi, vj, any_near, r2, ui, uj);
+    }
   } else if (BLOCK == UF_UT) {   // u = UF f + UT (t / a): the two share the geometry and both rsqrt (common subexpressions)
     pair_uf_wall_sym<T, BOTH>(rx, ry, rz, Rz, hi, hj, hi2, hi4, C, vi, vj, any_near, r2, ui, uj);
     pair_ut_wall_sym<T, BOTH>(rx, ry, rz, Rz, hi, hj, hi4, C, vi + 3, vj + 3, any_near, r2, ui, uj);
@@ -664,13 +673,12 @@ int make_plan(int block, int precision, long n_tgt, long n_src, const double* L,
   return 0;
 }
 
-// The pair-symmetric kernel exists for UF (wall or no wall) and UT / WF / WT / fused UF+UT (wall), fp64, every blob a target, open
+// The pair-symmetric kernel exists for UF / UT / WF / WT / fused UF+UT, single wall or no wall, fp64, every blob a target, open
 // or pseudo-periodic in x/y (a periodic z breaks |R|^2 = r^2 + 4 h_i h_j).  Forced by RMB_SYMMETRIC, chosen by default from
 // RMB_SYMMETRIC_MIN_N blobs on (below that the row kernel is as fast), never with RMB_DETERMINISTIC.
 bool use_symmetric(int block, int wall, int precision, int flags, long n_tgt, long n_src, const double* L)
 {
-  const bool blk = (block == RMB_UF && (wall == RMB_SINGLE_WALL || wall == RMB_NO_WALL)) ||
-                   ((block == RMB_UT || block == RMB_WF || block == RMB_WT || block == RMB_UF_UT) && wall == RMB_SINGLE_WALL);
+  const bool blk = block >= RMB_UF && block <= RMB_UF_UT && (wall == RMB_SINGLE_WALL || wall == RMB_NO_WALL);
   const bool ok = blk && precision == RMB_FP64 &&
                   !(L && L[2] > 0) && n_tgt == n_src && TILE % (TPB * RMB_SYM_NT) == 0;
   const bool want = (flags & RMB_SYMMETRIC) || (!(flags & RMB_DETERMINISTIC) && n_src >= RMB_SYMMETRIC_MIN_N);
@@ -770,23 +778,28 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
     A.n_split = split;
     const dim3 grid((unsigned)rows, (unsigned)split);
     constexpr int NT = RMB_SYM_NT;
+#define RMB_SYM_LAUNCH(B)                                                                  \
+    do {                                                                                   \
+      if (wall && per) sym_kernel<B, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);   \
+      else if (wall) sym_kernel<B, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);    \
+      else if (per) sym_kernel<B, true, NT, false, true><<<grid, TPB, 0, c.stream>>>(A);     \
+      else sym_kernel<B, true, NT, false, false><<<grid, TPB, 0, c.stream>>>(A);             \
+    } while (0)
     if (c.block == RMB_UF_UT) {
-      if (per) sym_kernel<UF_UT, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
-      else sym_kernel<UF_UT, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
-    } else if (c.block == RMB_UT) {
-      if (per) sym_kernel<UT, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
-      else sym_kernel<UT, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
+      RMB_SYM_LAUNCH(UF_UT);
+    } else if (c.block == RMB_WT) {
+      RMB_SYM_LAUNCH(WT);
+    } else if (c.block == RMB_UT || (c.block == RMB_WF && !wall)) {   // free space: WF is the same function as UT
+      RMB_SYM_LAUNCH(UT);
     } else if (c.block == RMB_WF) {
       if (per) sym_kernel<WF, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
       else sym_kernel<WF, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
-    } else if (c.block == RMB_WT) {
-      if (per) sym_kernel<WT, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
-      else sym_kernel<WT, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
     } else if (per && wall) sym_kernel<UF, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
     else if (per) sym_kernel<UF, true, NT, false, true><<<grid, TPB, 0, c.stream>>>(A);
     else if (!wall) sym_kernel<UF, true, NT, false, false><<<grid, TPB, 0, c.stream>>>(A);
     else if (c.flags & RMB_NO_TMA) sym_kernel<UF, false, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
     else sym_kernel<UF, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
+#undef RMB_SYM_LAUNCH
   }
   e = cudaGetLastError();
   if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: launch");
@@ -804,11 +817,12 @@ int sym_finish(const Call& c, const double* acc)
   const double norm = block_norm(c.block, c.eta, c.a);
 #define RMB_SYM_FINISH(B, W) sym_finish_kernel<B, W><<<nb, 128, 0, c.stream>>>( \
       reinterpret_cast<const SrcRec<double, SymRec<B>::NV>*>(c.ws), acc, damp, c.tgt_off, c.n_tgt, norm, in_plane, zscale, c.out)
-  if (c.block == RMB_UF_UT) RMB_SYM_FINISH(UF_UT, true);
-  else if (c.block == RMB_UT) RMB_SYM_FINISH(UT, true);
-  else if (c.block == RMB_WF) RMB_SYM_FINISH(WF, true);
-  else if (c.block == RMB_WT) RMB_SYM_FINISH(WT, true);
-  else if (c.wall == RMB_SINGLE_WALL) RMB_SYM_FINISH(UF, true);
+  const bool wall = c.wall == RMB_SINGLE_WALL;
+  if (c.block == RMB_UF_UT) { if (wall) RMB_SYM_FINISH(UF_UT, true); else RMB_SYM_FINISH(UF_UT, false); }
+  else if (c.block == RMB_UT) { if (wall) RMB_SYM_FINISH(UT, true); else RMB_SYM_FINISH(UT, false); }
+  else if (c.block == RMB_WF) { if (wall) RMB_SYM_FINISH(WF, true); else RMB_SYM_FINISH(WF, false); }
+  else if (c.block == RMB_WT) { if (wall) RMB_SYM_FINISH(WT, true); else RMB_SYM_FINISH(WT, false); }
+  else if (wall) RMB_SYM_FINISH(UF, true);
   else RMB_SYM_FINISH(UF, false);
 #undef RMB_SYM_FINISH
   const cudaError_t e = cudaGetLastError();
@@ -933,8 +947,8 @@ static int sym_call(Call& c, int block, int wall, int flags, long n, const doubl
 {
   if (n <= 0) return fail(RMB_E_ARG, "n must be positive");
   if (block < RMB_UF || block > RMB_UF_UT) return fail(RMB_E_ARG, "block must be RMB_UF..RMB_UF_UT");
-  if (wall != RMB_SINGLE_WALL && !(wall == RMB_NO_WALL && block == RMB_UF))
-    return fail(RMB_E_ARG, "the pair-symmetric product exists for RMB_SINGLE_WALL (all blocks) and RMB_NO_WALL (RMB_UF)");
+  if (wall != RMB_SINGLE_WALL && wall != RMB_NO_WALL)
+    return fail(RMB_E_ARG, "the pair-symmetric product exists for RMB_SINGLE_WALL and RMB_NO_WALL");
   if (L && L[2] > 0) return fail(RMB_E_ARG, "the pair-symmetric product cannot be periodic in z");
   if (!workspace) return fail(RMB_E_ARG, "null device pointer");
   if (!(a > 0) || !(eta > 0)) return fail(RMB_E_ARG, "a and eta must be positive");

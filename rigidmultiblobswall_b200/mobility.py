@@ -146,9 +146,8 @@ def _length3(periodic_length):
 def symmetric_partial(r_vectors, force, eta, a, rank=0, world=1, acc=None, flags=0, wall=SINGLE_WALL,
                       periodic_length=None, block=UF, vec_b=None):
     """Multi-rank pair-symmetric product, step 1 (rmb_symmetric_partial): this rank's share of the unordered
-    pairs, raw sums for ALL blobs -> acc (device tensor, summed over the ranks by the caller).  block = UF with
-    wall = SINGLE_WALL or NO_WALL, or UT / WF / WT / UF_UT (vec_b = torque) with SINGLE_WALL; periodic_length may be
-    periodic in x and/or y only."""
+    pairs, raw sums for ALL blobs -> acc (device tensor, summed over the ranks by the caller).  block = UF / UT / WF /
+    WT / UF_UT (vec_b = torque), wall = SINGLE_WALL or NO_WALL; periodic_length may be periodic in x and/or y only."""
     lib = _lib.load()
     dev = _device(r_vectors.device if isinstance(r_vectors, torch.Tensor) else None)
     n = (r_vectors.numel() if isinstance(r_vectors, torch.Tensor) else np.asarray(r_vectors).size) // 3

@@ -85,13 +85,12 @@ class ShardedMobility:
             self.block, self.wall, r, v, self.eta, self.a, periodic_length=self.L, precision=self.precision,
             targets=targets))
 
-        # Pair-symmetric schedule (UF wall / no wall, UT / WF / WT wall; fp64, not periodic in z): the unordered pairs are dealt to the
+        # Pair-symmetric schedule (UF / UT / WF / WT, wall or no wall; fp64, not periodic in z): the unordered pairs are dealt to the
         # ranks row group by row group, every rank accumulates raw sums for ALL blobs, the sums are all-reduced
         # (the one extra data-path collective: 24 N bytes) and each rank finishes its own target range.
         open_z = periodic_length is None or not bool(np.asarray(
             periodic_length.cpu() if isinstance(periodic_length, torch.Tensor) else periodic_length).reshape(-1)[2] > 0)
-        eligible = ((block == _mb.UF and wall in (_mb.SINGLE_WALL, _mb.NO_WALL)) or
-                    (block in (_mb.UT, _mb.WF, _mb.WT) and wall == _mb.SINGLE_WALL))
+        eligible = block in (_mb.UF, _mb.UT, _mb.WF, _mb.WT) and wall in (_mb.SINGLE_WALL, _mb.NO_WALL)
         self.symmetric = (symmetric is not False and local_product is None and eligible and
                           precision == _mb.FP64 and open_z and
                           (symmetric is True or n >= 16384))

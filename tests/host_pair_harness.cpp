@@ -240,12 +240,16 @@ extern "C" void host_sym_periodic(int block, int wall, long n, const double* r, 
         if (i == j) {     // own image: one direction (the opposite one is box -b of the same loop)
           if (block == UF && wall) pair_uf_wall_sym<T, false>(bx, by, rz, hi + hj, hi, hj, C.ht2, C.ht4, C, vi, vj, nr, r2, ui, ui);
           else if (block == UF) pair_uf_free_sym<T, false>(bx, by, rz, C, vi, vj, nr, r2, ui, ui);
+          else if (!wall && block == WT) pair_wt_free_sym<T, false>(bx, by, rz, C, vi, vj, nr, r2, ui, ui);
+          else if (!wall) pair_coupling_free_sym<T, false>(bx, by, rz, C, vi, vj, nr, r2, ui, ui);
           else if (block == WF) pair_wf_wall_sym<T, false>(bx, by, rz, hi + hj, hi, hj, C.ht4, C, vi, vj, nr, r2, ui, ui);
           else if (block == UT) pair_ut_wall_sym<T, false>(bx, by, rz, hi + hj, hi, hj, C.ht4, C, vi, vj, nr, r2, ui, ui);
           else pair_wt_wall_sym<T, false>(bx, by, rz, hi + hj, C.ht4, hj, C, vi, vj, nr, r2, ui, ui);
         } else {
           if (block == UF && wall) pair_uf_wall_sym<T, true>(bx, by, rz, hi + hj, hi, hj, C.ht2, C.ht4, C, vi, vj, nr, r2, ui, uj);
           else if (block == UF) pair_uf_free_sym<T, true>(bx, by, rz, C, vi, vj, nr, r2, ui, uj);
+          else if (!wall && block == WT) pair_wt_free_sym<T, true>(bx, by, rz, C, vi, vj, nr, r2, ui, uj);
+          else if (!wall) pair_coupling_free_sym<T, true>(bx, by, rz, C, vi, vj, nr, r2, ui, uj);
           else if (block == WF) pair_wf_wall_sym<T, true>(bx, by, rz, hi + hj, hi, hj, C.ht4, C, vi, vj, nr, r2, ui, uj);
           else if (block == UT) pair_ut_wall_sym<T, true>(bx, by, rz, hi + hj, hi, hj, C.ht4, C, vi, vj, nr, r2, ui, uj);
           else pair_wt_wall_sym<T, true>(bx, by, rz, hi + hj, C.ht4, hj, C, vi, vj, nr, r2, ui, uj);
@@ -263,7 +267,8 @@ extern "C" void host_sym_periodic(int block, int wall, long n, const double* r, 
       case UT * 2 + 1: self_apply<T, UT, true>(h, rec[i].v, ux, uy, uz); break;
       case WF * 2 + 1: self_apply<T, WF, true>(h, rec[i].v, ux, uy, uz); break;
       case WT * 2 + 1: self_apply<T, WT, true>(h, rec[i].v, ux, uy, uz); break;
-      default: break;
+      case WT * 2: self_apply<T, WT, false>(h, rec[i].v, ux, uy, uz); break;
+      default: break;     // no_wall UT / WF: no self term
     }
     out[3 * i] = ux * norm * damp[i]; out[3 * i + 1] = uy * norm * damp[i]; out[3 * i + 2] = uz * norm * damp[i];
   }

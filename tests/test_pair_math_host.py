@@ -183,3 +183,6 @@ def test_pair_symmetric_rotation_blocks(golden, harness, cloud, lname, block):
     a, eta = golden[f"{cloud}/a_eta"]
     L = golden[f"{cloud}/L_{lname}"]
     assert relerr(harness.sym_periodic(r, v, eta, a, L, block=block), golden[f"{cloud}/{lname}/single_wall/{block}"]) < 1e-12
+    # free-space twins (pair_coupling_free_sym, pair_wt_free_sym)
+    assert relerr(harness.sym_periodic(r, v, eta, a, L, wall=False, block=block),
+                  golden[f"{cloud}/{lname}/no_wall/{block}"]) < 1e-12
