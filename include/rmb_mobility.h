@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define RMB_VERSION 104 /* 0.1.1 */
+#define RMB_VERSION 105 /* 0.1.2: pair-symmetric kernels also for the RMB_NO_WALL rotation blocks */
 
 /* block: which mobility block is applied (mobility.py naming in comments) */
 #define RMB_UF 0    /* *_mobility_trans_times_force        (mobility.py:222,288,1119,1132) */
@@ -57,9 +57,9 @@ extern "C" {
 #define RMB_IN_PLANE 1    /* in_plane_* (mobility.py:255,454,1166,1235): z column and row zero */
 #define RMB_NO_TMA 2      /* stage source tiles with plain loads instead of cp.async.bulk (debug) */
 #define RMB_SYMMETRIC 4   /* evaluate every unordered pair once and update both blobs.  Exists for fp64, n_targets ==
-                             n_sources, L[2] <= 0 (open or pseudo-periodic in x / y), and RMB_UF (single wall or no
-                             wall) or RMB_UT / RMB_WF / RMB_WT / RMB_UF_UT (single wall); any other call ignores the
-                             flag and takes the row kernel.  Sums are accumulated with atomics: results agree with
+                             n_sources, L[2] <= 0 (open or pseudo-periodic in x / y), blocks RMB_UF / RMB_UT / RMB_WF /
+                             RMB_WT / RMB_UF_UT with RMB_SINGLE_WALL or RMB_NO_WALL; any other call (fp32, free
+                             surface, target shards, periodic z) ignores the flag and takes the row kernel.  Sums are accumulated with atomics: results agree with
                              the row kernel to rounding, but are not bit-reproducible run to run.  Without this
                              flag the symmetric kernel is still chosen for eligible calls with
                              n_sources >= RMB_SYMMETRIC_MIN_N */
@@ -113,8 +113,8 @@ int rmb_mobility_product(int block, int wall, int precision, int flags,
                          double *out, void *workspace, size_t workspace_bytes, void *stream);
 
 /*
- * Multi-rank form of the pair-symmetric product (fp64; block = RMB_UF with wall = RMB_SINGLE_WALL or RMB_NO_WALL,
- * or block = RMB_UT / RMB_WF / RMB_WT / RMB_UF_UT with RMB_SINGLE_WALL (vec_b = torque for RMB_UF_UT, else NULL);
+ * Multi-rank form of the pair-symmetric product (fp64; block = RMB_UF / RMB_UT / RMB_WF / RMB_WT / RMB_UF_UT
+ * (vec_b = torque for RMB_UF_UT, else NULL), wall = RMB_SINGLE_WALL or RMB_NO_WALL;
  * all n blobs targets and sources; L = NULL or
  * pseudo-periodic in x and/or y only: L[2] must be 0).  Every rank calls
  *   rmb_symmetric_partial()  raw pair sums, for ALL blobs, of this rank's share of the unordered pairs (row groups

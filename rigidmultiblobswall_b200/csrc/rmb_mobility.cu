@@ -10,8 +10,8 @@
 //                    (cp.async.bulk + mbarrier, 2 stages); FP64 or FP32
 //   finish_kernel  : O(N n_split) -- sum of source-split partials, self term,
 //                    normalisation, damping B, in-plane mask
-//   sym_kernel     : O(N^2 n_boxes / 2) -- the flagship (UF and, with a wall,
-//                    UT / WF / WT; fp64, wall or no
+//   sym_kernel     : O(N^2 n_boxes / 2) -- the flagship (UF / UT / WF / WT and
+//                    the fused UF+UT; fp64, wall or no
 //                    wall, open or pseudo-periodic in x / y, all blobs targets):
 //                    every unordered pair once, both blobs updated;
 //                    sym_finish_kernel closes it

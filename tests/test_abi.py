@@ -29,7 +29,7 @@ def test_library_exports_every_declared_symbol():
 def test_version_and_argument_errors_without_gpu():
     from rigidmultiblobswall_b200 import _lib
     lib = _lib.load()
-    assert lib.rmb_version() == 104
+    assert lib.rmb_version() == 105
     # argument validation happens before any CUDA call
     rc = lib.rmb_mobility_product(99, 0, 0, 0, 1, 1, 0, None, None, None, 1.0, 1.0, None, None, None, 0, None)
     assert rc == -1 and b"block" in lib.rmb_last_error()
