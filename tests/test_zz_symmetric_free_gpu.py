@@ -13,9 +13,10 @@ TOL64 = 1e-12
 BLOCK_ID = {"UF": 0, "UT": 1, "WF": 2, "WT": 3}
 
 
-def relerr(x, ref):
-    nrm = np.linalg.norm(ref)       # a lone blob in free space: UT / WF give exactly 0 (no self term)
-    return np.linalg.norm(np.asarray(x) - ref) / (nrm if nrm > 0 else 1.0)
+def relerr(x, ref, floor=0.0):
+    """norm-wise relative error; `floor` is the magnitude below which the reference itself is cancellation noise
+    (a lone blob in free space: UT / WF give exactly 0, and its periodic images cancel pairwise to ~1e-18)"""
+    return np.linalg.norm(np.asarray(x) - ref) / max(np.linalg.norm(ref), floor, 1e-300)
 
 
 @pytest.fixture(scope="module")
@@ -54,7 +55,7 @@ def test_ragged_vs_oracle(mb, n):
         ref = {blk: oracle.mobility_product(blk, "no_wall", r, v, eta, a, periodic_length=L) for blk in ("UT", "WF", "WT")}
         for blk in ("UT", "WF", "WT"):
             out = mb.mobility_product(BLOCK_ID[blk], mb.NO_WALL, r, v, eta, a, periodic_length=L, flags=mb.SYMMETRIC)
-            assert relerr(out, ref[blk]) < TOL64, (blk, L)
+            assert relerr(out, ref[blk], floor=np.linalg.norm(v) / (8 * np.pi * eta * a ** 2)) < TOL64, (blk, L)
         fused = oracle.mobility_product("UF", "no_wall", r, v, eta, a, periodic_length=L) + \
             oracle.mobility_product("UT", "no_wall", r, t, eta, a, periodic_length=L)
         out = mb.mobility_product(mb.UF_UT, mb.NO_WALL, r, v, eta, a, periodic_length=L, vec_b=t, flags=mb.SYMMETRIC)
