@@ -247,10 +247,13 @@ def build_block_diagonal_preconditioner(bodies, r_vectors, Nblobs, eta, a, *args
 
 
 def solve_mobility_problem(bodies, force_torque, eta, a, tolerance=1e-8, periodic_length=None, slip=None,
-                           PC=None, restart=60, maxiter=1000, callback=None, mobility_vector_prod=None, wall=True):
+                           PC=None, restart=60, maxiter=1000, callback=None, mobility_vector_prod=None, wall=True,
+                           x0=None):
     """The `mobility` scheme of multi_bodies_utilities.py:420-540 (free rigid bodies) on the device:
     RHS = [slip ; -force_torque] scaled to unit norm, right-preconditioned GMRES(60) on
     linear_operator_rigid with the block-diagonal preconditioner, solution rescaled.
+    x0: optional first guess [lambda ; U] (e.g. the previous time step's solution, as the reference's integrators
+    pass it, quaternion_integrator_multi_bodies.py:1525).
     Returns (velocity [Nbodies, 6], lambda_blobs [Nblobs, 3], iterations, info)."""
     from . import solvers
     dev = bodies.device
@@ -270,7 +273,10 @@ def solve_mobility_problem(bodies, force_torque, eta, a, tolerance=1e-8, periodi
         mobility_vector_prod = (mobility.single_wall_mobility_trans_times_force_b200 if wall
                                 else mobility.no_wall_mobility_trans_times_force_b200)
     A = lambda v: linear_operator_rigid(v, bodies, r, eta, a, mobility_vector_prod, periodic_length=periodic_length)
-    x, info, its = solvers.gmres(A, rhs, tol=tolerance, restart=restart, maxiter=maxiter, M=PC, callback=callback)
+    if x0 is not None:
+        x0 = torch.as_tensor(x0, dtype=torch.float64).to(dev).reshape(-1)
+        x0 = x0 / nrm if float(nrm) > 0 else x0
+    x, info, its = solvers.gmres(A, rhs, x0=x0, tol=tolerance, restart=restart, maxiter=maxiter, M=PC, callback=callback)
     if float(nrm) > 0:
         x = x * nrm
     return x[n3:].reshape(-1, 6), x[:n3].reshape(-1, 3), its, info

@@ -35,7 +35,8 @@ def gmres(A, b, x0=None, tol=1e-5, restart=60, maxiter=None, M=None, callback=No
     Returns (x, info, iterations); info = 0 on convergence, else the iteration count (SciPy's convention).
     Convergence: ||b - A x|| <= max(atol, tol*||b||), tested on the Givens residual estimate every
     inner iteration like scipy.sparse.linalg.gmres; callback(residual_norm/||b||) once per inner iteration.
-    maxiter counts restart cycles (SciPy >= 1.12 semantics)."""
+    maxiter counts restart cycles (SciPy >= 1.12 semantics).  x0: initial guess for x (not for the preconditioned
+    variable); a good guess saves iterations because the target stays max(atol, tol*||b||)."""
     n = b.numel()
     dev, dt = b.device, b.dtype
     if maxiter is None:
@@ -46,9 +47,16 @@ def gmres(A, b, x0=None, tol=1e-5, restart=60, maxiter=None, M=None, callback=No
         return torch.zeros_like(b), 0, 0
     target = max(float(atol), tol * bnorm)
     apply_AM = (lambda v: A(M(v))) if M is not None else A
-    y = torch.zeros_like(b)                    # solution of A P^-1 y = b
     if x0 is not None:
-        raise NotImplementedError("x0 is applied by the caller (reference passes x0 in the unpreconditioned variable)")
+        # Initial guess, in the unpreconditioned variable: solve A dx = b - A x0 to the SAME absolute target, add.
+        # (The reference's right-preconditioned wrapper drops x0, general_application_utils.py:627.)
+        r0 = b - A(x0)
+        scale = float(_norm(r0, group)) / bnorm
+        cb = None if callback is None else (lambda rel: callback(rel * scale))     # residuals stay relative to ||b||
+        dx, info, its = gmres(A, r0, tol=0.0, restart=restart, maxiter=maxiter, M=M, callback=cb, atol=target,
+                              group=group)
+        return x0 + dx, info, its
+    y = torch.zeros_like(b)                    # solution of A P^-1 y = b
     V = torch.empty(restart + 1, n, dtype=dt, device=dev)
     its = 0
     r = b.clone()

@@ -49,6 +49,26 @@ def test_gmres_zero_rhs_and_no_preconditioner():
     assert info == 0 and torch.allclose(x, b / 2)
 
 
+def test_gmres_initial_guess():
+    rng = np.random.default_rng(3)
+    n = 200
+    A = torch.from_numpy(rng.standard_normal((n, n)) / np.sqrt(n) + 3.0 * np.eye(n))
+    P = torch.diag(1.0 / torch.diag(A))
+    b = torch.from_numpy(rng.standard_normal(n))
+    x, info, its = solvers.gmres(lambda v: A @ v, b, tol=1e-10, restart=30, M=lambda v: P @ v)
+    assert info == 0
+    # exact solution as the guess: nothing to do; a perturbed one: fewer iterations, same answer, same target
+    xe, info_e, its_e = solvers.gmres(lambda v: A @ v, b, x0=x, tol=1e-9, restart=30, M=lambda v: P @ v)
+    assert info_e == 0 and its_e == 0 and torch.equal(xe, x)
+    res = []
+    x0 = x + 1e-4 * torch.from_numpy(rng.standard_normal(n))
+    x2, info2, its2 = solvers.gmres(lambda v: A @ v, b, x0=x0, tol=1e-10, restart=30, M=lambda v: P @ v, callback=res.append)
+    assert info2 == 0 and 0 < its2 < its and len(res) == its2
+    assert float(torch.linalg.norm(A @ x2 - b) / torch.linalg.norm(b)) < 2e-10
+    assert res[-1] <= 1e-10 and res[0] < 1e-3        # callbacks report residuals relative to ||b||
+    assert float(torch.linalg.norm(x2 - x) / torch.linalg.norm(x)) < 1e-9
+
+
 def test_gmres_reports_non_convergence():
     rng = np.random.default_rng(1)
     A = torch.from_numpy(rng.standard_normal((50, 50)))

@@ -71,3 +71,14 @@ def test_body_mobility(gold, setup):
     assert tuple(N.shape) == (72, 72)
     assert relerr(N, g["body_mobility/N"]) < 1e-8
     assert relerr(N, N.T.cpu().numpy()) < 1e-8
+
+
+def test_mobility_problem_first_guess(gold, setup):
+    """x0 = a previous solution (what the reference's integrators pass): fewer iterations, same answer"""
+    rg, _ = gold
+    rigid, bodies, PC, eta, a = setup
+    vel, lam, its, info = rigid.solve_mobility_problem(bodies, rg["rigid/FT"], eta, a, tolerance=1e-8, PC=PC)
+    guess = torch.cat([lam.reshape(-1), vel.reshape(-1)]) * (1 + 1e-3)
+    vel2, lam2, its2, info2 = rigid.solve_mobility_problem(bodies, rg["rigid/FT"], eta, a, tolerance=1e-8, PC=PC, x0=guess)
+    assert info == 0 and info2 == 0 and its2 < its
+    assert relerr(torch.cat([lam2.reshape(-1), vel2.reshape(-1)]), rg["rigid/solution"]) < 1e-6
