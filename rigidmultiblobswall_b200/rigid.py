@@ -7,8 +7,8 @@ iteration as interpreted loops over bodies:
 
     K_matrix_vector_prod              multi_bodies.py:328-347
     K_matrix_T_vector_prod            multi_bodies.py:350-371
-    linear_operator_rigid             multi_bodies.py:424-471  (no constraints, no prescribed kinematics)
-    build_block_diagonal_preconditioner  multi_bodies.py:752-903 (free bodies)
+    linear_operator_rigid             multi_bodies.py:424-471  (free and prescribed-kinematics bodies; no articulated constraints)
+    build_block_diagonal_preconditioner  multi_bodies.py:752-903 (same)
     solve_mobility_problem / solve_resistance_problem / body_mobility
                                       the `mobility`, `resistance` and `body_mobility` schemes of
                                       multi_bodies_utilities.py:449-540, :549-574, :576-600
@@ -52,7 +52,7 @@ class RigidBodies:
     (s, p1, p2, p3) and reference configuration (body/body.py:17-40).  Body b
     owns the contiguous blob range [body_offset[b], body_offset[b+1])."""
 
-    def __init__(self, reference_configurations, locations, quaternions, device=None):
+    def __init__(self, reference_configurations, locations, quaternions, device=None, prescribed_velocity=None):
         dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.device = dev
         if isinstance(reference_configurations, np.ndarray) and reference_configurations.ndim == 2:
@@ -73,12 +73,33 @@ class RigidBodies:
         self.reference_configuration = torch.from_numpy(np.ascontiguousarray(ref)).to(dev)
         self.location = torch.as_tensor(np.asarray(locations, dtype=np.float64).reshape(-1, 3)).to(dev).contiguous()
         self.quaternion = torch.as_tensor(np.asarray(quaternions, dtype=np.float64).reshape(-1, 4)).to(dev).contiguous()
+        self.set_prescribed(prescribed_velocity)
+
+    def set_prescribed(self, prescribed_velocity):
+        """Bodies with prescribed kinematics (body.py:58-59, :150): prescribed_velocity is None (all bodies free) or
+        a sequence with one entry per body, None for a free body, else its 6 prescribed components (U, omega)."""
+        nb = self.n_bodies
+        mask = np.zeros(nb, dtype=bool)
+        vel = np.zeros((nb, 6))
+        if prescribed_velocity is not None:
+            if len(prescribed_velocity) != nb:
+                raise ValueError("prescribed_velocity needs one entry (None or 6 numbers) per body")
+            for k, v in enumerate(prescribed_velocity):
+                if v is not None:
+                    mask[k] = True
+                    vel[k] = np.asarray(v, dtype=np.float64).reshape(6)
+        self.any_prescribed = bool(mask.any())
+        self.prescribed = torch.from_numpy(mask).to(self.device)
+        self.prescribed_velocity = torch.from_numpy(vel).to(self.device)
 
     @classmethod
     def from_bodies(cls, bodies, device=None):
         """From the reference's own list of body.Body objects."""
+        presc = [b.calc_prescribed_velocity() if getattr(b, "prescribed_kinematics", False) is True else None
+                 for b in bodies]
         return cls([b.reference_configuration for b in bodies], [b.location for b in bodies],
-                   [b.orientation.entries for b in bodies], device=device)
+                   [b.orientation.entries for b in bodies], device=device,
+                   prescribed_velocity=presc if any(p is not None for p in presc) else None)
 
     def get_r_vectors(self):
         """multi_bodies.get_blobs_r_vectors (multi_bodies.py:196-208): flat 3*Nblobs tensor."""
@@ -118,14 +139,24 @@ def K_matrix_T_vector_prod(bodies, vector, Nblobs=None, K_bodies=None, r_vectors
 
 
 def linear_operator_rigid(vector, bodies, r_vectors, eta, a, mobility_vector_prod=None, *args, **kwargs):
-    """Action of  |  M   -K | on [lambda; U]  (multi_bodies.py:424-471, free bodies, no constraints).
+    """Action of  |  M   -K | on [lambda; U]  (multi_bodies.py:424-471, no articulated constraints).
                   | -K^T  0 |
+    For a body with prescribed kinematics (:458-464) the unknown in its U slot is the force-torque it needs: its
+    K U term drops out of the blob rows and its body rows read -K^T lambda + F.
     mobility_vector_prod defaults to the single-wall B200 product."""
     mvp = mobility.single_wall_mobility_trans_times_force_b200 if mobility_vector_prod is None else mobility_vector_prod
     n3 = 3 * bodies.n_blobs
     res = torch.empty_like(vector)
     lam, U = vector[:n3], vector[n3:]
     res[:n3] = mvp(r_vectors, lam, eta, a, *args, **kwargs)
+    if bodies.any_prescribed:
+        pm = bodies.prescribed.unsqueeze(1)
+        U2 = U.reshape(-1, 6)
+        K_matrix_vector_prod(bodies, torch.where(pm, torch.zeros_like(U2), U2), r_vectors=r_vectors, out=res[:n3],
+                             alpha=-1.0, beta=1.0)
+        ktl = K_matrix_T_vector_prod(bodies, lam, r_vectors=r_vectors, alpha=-1.0).reshape(-1, 6)
+        res[n3:] = torch.where(pm, ktl + U2, ktl).reshape(-1)
+        return res
     K_matrix_vector_prod(bodies, U, r_vectors=r_vectors, out=res[:n3], alpha=-1.0, beta=1.0)
     res[n3:] = K_matrix_T_vector_prod(bodies, lam, r_vectors=r_vectors, alpha=-1.0).reshape(-1)
     return res
@@ -138,8 +169,9 @@ class BlockDiagonalPreconditioner:
         M_b  dense blob mobility of the body alone (rmb_body_mobility_blocks)
         M_b^-1  via batched Cholesky (torch.linalg.cholesky + cholesky_inverse: plain library calls)
         N_b = pinv(K_b^T M_b^-1 K_b)   (6x6)
-    apply (multi_bodies.py:825-846), per body:
+    apply (multi_bodies.py:825-862), per body:
         Lambda~ = M_b^-1 slip;  U = N_b (-F - K^T Lambda~);  Lambda = M_b^-1 (slip + K U)
+        (prescribed kinematics: Lambda = Lambda~, and the body slot returns the force K^T Lambda)
     Bodies with fewer blobs than nb_max are identity-padded (the padding rows
     never couple to real ones)."""
 
@@ -196,8 +228,13 @@ class BlockDiagonalPreconditioner:
         slip = self._pad(vector[:n3]).unsqueeze(2)                 # [nb, m, 1]
         F = vector[n3:].reshape(nb, 6, 1)
         lam_t = self.M_inv @ slip
-        U = self.N @ (-F - self.K.transpose(1, 2) @ lam_t)
+        KT_lam_t = self.K.transpose(1, 2) @ lam_t
+        U = self.N @ (-F - KT_lam_t)
         lam = self.M_inv @ (slip + self.K @ U)
+        if self.bodies.any_prescribed:          # multi_bodies.py:850-862: Lambda = M_b^-1 (slip + K U), F = K^T Lambda
+            pm = self.bodies.prescribed.reshape(nb, 1, 1)
+            lam = torch.where(pm, lam_t, lam)
+            U = torch.where(pm, KT_lam_t, U)
         out = torch.empty_like(vector)
         out[:n3] = self._unpad(lam.squeeze(2))
         out[n3:] = U.reshape(-1)
@@ -252,6 +289,8 @@ def solve_mobility_problem(bodies, force_torque, eta, a, tolerance=1e-8, periodi
     """The `mobility` scheme of multi_bodies_utilities.py:420-540 (free rigid bodies) on the device:
     RHS = [slip ; -force_torque] scaled to unit norm, right-preconditioned GMRES(60) on
     linear_operator_rigid with the block-diagonal preconditioner, solution rescaled.
+    Bodies with prescribed kinematics (RigidBodies.set_prescribed) keep their velocity; the force-torque they need is
+    K^T lambda (K_matrix_T_vector_prod) restricted to them.
     x0: optional first guess [lambda ; U] (e.g. the previous time step's solution, as the reference's integrators
     pass it, quaternion_integrator_multi_bodies.py:1525).
     Returns (velocity [Nbodies, 6], lambda_blobs [Nblobs, 3], iterations, info)."""
@@ -264,6 +303,10 @@ def solve_mobility_problem(bodies, force_torque, eta, a, tolerance=1e-8, periodi
     if slip is not None:
         rhs[:n3] = torch.as_tensor(slip, dtype=torch.float64).to(dev).reshape(-1)
     rhs[n3:] = -FT
+    if bodies.any_prescribed:                  # multi_bodies_utilities.py:481-489: RHS += K U_prescribed, F rows = 0
+        K_matrix_vector_prod(bodies, bodies.prescribed_velocity, r_vectors=r, out=rhs[:n3], alpha=1.0, beta=1.0)
+        rhs[n3:] = torch.where(bodies.prescribed.unsqueeze(1), torch.zeros_like(FT.reshape(-1, 6)),
+                               -FT.reshape(-1, 6)).reshape(-1)
     nrm = torch.linalg.norm(rhs)
     if float(nrm) > 0:
         rhs = rhs / nrm
@@ -279,7 +322,10 @@ def solve_mobility_problem(bodies, force_torque, eta, a, tolerance=1e-8, periodi
     x, info, its = solvers.gmres(A, rhs, x0=x0, tol=tolerance, restart=restart, maxiter=maxiter, M=PC, callback=callback)
     if float(nrm) > 0:
         x = x * nrm
-    return x[n3:].reshape(-1, 6), x[:n3].reshape(-1, 3), its, info
+    velocity = x[n3:].reshape(-1, 6)
+    if bodies.any_prescribed:                  # :524-527: those bodies move as prescribed (their slot held the force)
+        velocity = torch.where(bodies.prescribed.unsqueeze(1), bodies.prescribed_velocity, velocity)
+    return velocity, x[:n3].reshape(-1, 3), its, info
 
 
 def solve_resistance_problem(bodies, velocity, eta, a, tolerance=1e-8, periodic_length=None, slip=None,

@@ -82,3 +82,25 @@ def test_mobility_problem_first_guess(gold, setup):
     vel2, lam2, its2, info2 = rigid.solve_mobility_problem(bodies, rg["rigid/FT"], eta, a, tolerance=1e-8, PC=PC, x0=guess)
     assert info == 0 and info2 == 0 and its2 < its
     assert relerr(torch.cat([lam2.reshape(-1), vel2.reshape(-1)]), rg["rigid/solution"]) < 1e-6
+
+
+def test_prescribed_kinematics(gold):
+    """bodies 2 and 7 move as prescribed (mixed mobility / resistance problem): operator, preconditioner and the
+    `mobility` scheme against the reference (tests/golden/prescribed_golden.npz, make_golden_prescribed.py)"""
+    from rigidmultiblobswall_b200 import rigid
+    rg, _ = gold
+    g = np.load(os.path.join(HERE, "golden", "prescribed_golden.npz"))
+    a, eta, _ = rg["rigid/a_eta_tol"]
+    presc = [g["prescribed_velocity"][k] if g["prescribed"][k] else None for k in range(12)]
+    bodies = rigid.RigidBodies(rg["struct/boomerang_N_15"], rg["rigid/location"], rg["rigid/quaternion"],
+                               prescribed_velocity=presc)
+    assert bodies.any_prescribed
+    r = bodies.get_r_vectors()
+    x = torch.from_numpy(g["x"]).cuda()
+    assert relerr(rigid.linear_operator_rigid(x, bodies, r, eta, a), g["A_x"]) < 1e-12
+    PC = rigid.BlockDiagonalPreconditioner(bodies, r, eta, a)
+    assert relerr(PC(x), g["PC_x"]) < 1e-9
+    vel, lam, its, info = rigid.solve_mobility_problem(bodies, g["FT"], eta, a, tolerance=1e-10, slip=g["slip"], PC=PC)
+    assert info == 0 and abs(its - int(g["gmres_iterations"][0])) <= 1
+    assert relerr(vel, g["velocity"]) < 1e-8 and relerr(lam, g["lambda"]) < 1e-8
+    assert relerr(rigid.K_matrix_T_vector_prod(bodies, lam, r_vectors=r).reshape(-1, 6), g["force"]) < 1e-8
