@@ -43,10 +43,13 @@ def _device(dev=None):
 
 
 def _workspace(nbytes, dev):
-    ws = _workspaces.get(dev)
+    """Scratch buffer of the current stream on `dev` (one per (device, stream): products enqueued on different
+    streams may run concurrently and must not share records; on one stream they are ordered)."""
+    key = (dev, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=dev)
-        _workspaces[dev] = ws
+        _workspaces[key] = ws
     return ws
 
 
@@ -169,8 +172,8 @@ def symmetric_partial(r_vectors, force, eta, a, rank=0, world=1, acc=None, flags
 def symmetric_finish(n, acc, eta, a, targets=None, out=None, flags=0, wall=SINGLE_WALL, periodic_length=None,
                      block=UF):
     """Step 2 (rmb_symmetric_finish) after the ranks' acc have been summed: self term, normalisation, damping for
-    the target range.  Must follow symmetric_partial (same block, wall, a, periodic_length) on the same device: it reads
-    that call's workspace."""
+    the target range.  Must follow symmetric_partial (same block, wall, a, periodic_length) on the same device and
+    stream: it reads that call's workspace."""
     lib = _lib.load()
     dev = acc.device
     off, cnt = (0, n) if targets is None else targets
