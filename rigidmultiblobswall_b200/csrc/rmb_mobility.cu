@@ -322,10 +322,11 @@ __global__ void finish_kernel(const MfArgs<T, (BLOCK == UF_UT) ? 2 : 1> A)
   A.out[3 * li + 2] = A.in_plane ? 0.0 : dz * sc;
 }
 
-// ------------------------------------------------ pair-symmetric UF kernel --
-// Single-wall UF, open boundaries, all blobs both targets and sources: every
-// unordered pair is evaluated ONCE and updates both u_i and u_j
-// (pair_uf_wall_sym: 88 FP64 instructions for two interactions instead of 132).
+// --------------------------------------------------- pair-symmetric kernel --
+// All blobs both targets and sources (UF / UT / WF / WT / fused UF+UT, single
+// wall or no wall, open or pseudo-periodic in x / y): every unordered pair is
+// evaluated ONCE and updates both u_i and u_j (single-wall UF, pair_uf_wall_sym:
+// 88 FP64 instructions for two interactions instead of 132).
 //
 // Blobs are cut into blocks of 32.  A warp owns one block I (lane l holds blob
 // 32 I + l in registers) and sweeps the blocks J >= I of its source tiles.  In
@@ -740,7 +741,7 @@ int launch(const Call& c)
   return 0;
 }
 
-// Pair-symmetric path: UF, fp64, wall or no wall, not periodic in z, every blob a target.
+// Pair-symmetric path: every block, fp64, wall or no wall, not periodic in z, every blob a target.
 // Step 1: records + raw pair sums of the row groups row_first, row_first + row_stride, ... into acc.
 int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
 {
