@@ -1,7 +1,7 @@
 #!/bin/bash
-# First GPU call of a new round (one B200, ~12 min): everything this round could not run on the GPU because its
-# budget was spent -- the two rigid-scheme tests added last (first guess, prescribed kinematics), the full GPU
-# suite, smoke, bench + reference arm, and the symmetric/row crossover of the free-space rotation blocks at small N.
+# First GPU call of a new round (one B200, ~12 min): the tests added last in round 1 (each was run on a B200 on its
+# own; the Blake-limit invariant only on the oracle), the full GPU suite, smoke, bench + reference arm, and the
+# symmetric/row crossover of the free-space rotation blocks at small N.
 #   gpurun --timeout 1500 -- 'bash tools/gpu_round2_start.sh r02a'
 mkdir -p gpurun_out
 T=${1:-r02a}
