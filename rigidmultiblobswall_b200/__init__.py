@@ -7,4 +7,4 @@ mobility.py signatures, plus (later rows) the rigid-body operators around it.
 from . import _lib  # noqa: F401
 from . import mobility  # noqa: F401
 
-__version__ = "0.1.0"
+__version__ = "0.1.2"   # = RMB_VERSION 105 (include/rmb_mobility.h)
