@@ -150,3 +150,22 @@ def test_finite_size_limit_is_the_point_force_image_system(product):
             dn = np.linalg.norm(d)
             oseen = (np.eye(3) / dn + np.outer(d, d) / dn ** 3) / (8 * np.pi * eta)
             assert np.abs(mf[3 * i:3 * i + 3, 3 * j:3 * j + 3] - oseen).max() < 1e-10 * np.abs(oseen).max()
+
+
+@pytest.mark.parametrize("block", BLOCKS)
+def test_clamp_and_damping_are_B_M_B_also_below_the_wall_plane(product, block):
+    """mobility.py:52-84, 1152-1162: the wall forms compute B M(r_eff) (B v) with z_eff = max(z, a) and B_ii = z_i / a
+    for z_i < a -- also for z <= 0, where B <= 0 and the reference still 'works' (SURVEY 8b).  The fused clamp and
+    damping of the product must equal the explicit three steps on already-clamped positions."""
+    rng = np.random.default_rng(17)
+    n, a, eta = 200, 0.13, 7.0
+    r = 5 * a * rng.random((n, 3))
+    r[:, 2] -= 1.5 * a                                   # ~30 % of the blobs have z < 0, ~50 % z < a
+    assert (r[:, 2] < 0).sum() > 20
+    v = rng.standard_normal((n, 3))
+    B = np.where(r[:, 2] < a, r[:, 2] / a, 1.0)
+    r_eff = r.copy()
+    r_eff[:, 2] = np.maximum(r[:, 2], a)
+    fused = product(block, "single_wall", r, v, eta, a)
+    steps = np.repeat(B, 3) * product(block, "single_wall", r_eff, v * B[:, None], eta, a)
+    assert np.linalg.norm(fused - steps) <= 1e-13 * np.linalg.norm(steps)
