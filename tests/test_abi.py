@@ -39,6 +39,20 @@ def test_version_and_argument_errors_without_gpu():
     assert rc == -1 and b"wall" in lib.rmb_last_error()
     rc = lib.rmb_mobility_source_target(1, 0, 0, 3, 2, None, None, None, None, None, 1.0, None, 8, None, 0, None)
     assert rc == -1 and b"null" in lib.rmb_last_error()
+    # multi-rank pair-symmetric form: every block with a single wall or none; never a free surface or a periodic z
+    Lz = (ctypes.c_double * 3)(0.0, 0.0, 5.0)
+    p = 16      # a non-null "device pointer" that is never dereferenced: every call below fails validation first
+    rc = lib.rmb_symmetric_partial(1, 2, 0, 100, 0, 1, p, p, None, 1.0, 1.0, None, p, None, 0, None)
+    assert rc == -1 and b"RMB_NO_WALL" in lib.rmb_last_error()
+    rc = lib.rmb_symmetric_partial(3, 0, 0, 100, 0, 1, p, p, None, 1.0, 1.0, Lz, p, None, 0, None)
+    assert rc == -1 and b"periodic in z" in lib.rmb_last_error()
+    rc = lib.rmb_symmetric_partial(3, 0, 0, 100, 0, 1, p, p, None, 1.0, 1.0, None, p, None, 0, None)
+    assert rc == -1 and b"null" in lib.rmb_last_error()          # no_wall WT is a valid block: the workspace check fires
+    rc = lib.rmb_symmetric_partial(4, 0, 0, 100, 0, 1, p, p, None, 1.0, 1.0, None, p, None, 0, None)
+    assert rc == -1 and b"vec_b" in lib.rmb_last_error()
+    rc = lib.rmb_symmetric_partial(0, 1, 0, 100, 2, 2, p, p, None, 1.0, 1.0, None, p, None, 0, None)
+    assert rc == -1 and b"rank" in lib.rmb_last_error()
+    assert lib.rmb_symmetric_acc_len(1000) == 1024 * 3
 
 
 def test_python_api_mirrors_reference_names():
