@@ -208,6 +208,30 @@ class ShardedRigidSystem:
             x = x * nrm
         return x[self.n3:].reshape(-1, 6), x[:self.n3].reshape(-1, 3), its, info
 
+    def solve_resistance(self, velocity_loc, tolerance=1e-8, slip_loc=None, restart=60, maxiter=1000, callback=None):
+        """The resistance problem (multi_bodies_utilities.py:549-574) on sharded vectors, matrix-free:
+        M lambda = slip + K U with the local bodies' M_b^-1 as right preconditioner, F = K^T lambda.
+        velocity_loc: (U, omega) of this rank's bodies.  Returns (force_loc [nb_loc, 6], lambda_loc [n_loc, 3],
+        iterations, info)."""
+        from . import solvers
+        if self.PC is None:
+            self.build_preconditioner()
+        dev = self.r_full.device
+        U = torch.as_tensor(velocity_loc, dtype=torch.float64).to(dev).reshape(-1)
+        rhs = self.backend.K_matrix_vector_prod(self.bodies, U, r_vectors=self.r_loc).reshape(-1).clone()
+        if slip_loc is not None:
+            rhs += torch.as_tensor(slip_loc, dtype=torch.float64).to(dev).reshape(-1)
+        grp = self.group if self.world > 1 else None
+        nrm = _global_norm(rhs, grp)
+        if nrm > 0:
+            rhs = rhs / nrm
+        lam, info, its = solvers.gmres(lambda v: self.mobility(v).reshape(-1), rhs, tol=tolerance, restart=restart,
+                                       maxiter=maxiter, M=self.PC.M_inv_mult, callback=callback, group=grp)
+        if nrm > 0:
+            lam = lam * nrm
+        force = self.backend.K_matrix_T_vector_prod(self.bodies, lam, r_vectors=self.r_loc).reshape(-1, 6)
+        return force, lam.reshape(-1, 3), its, info
+
     def stochastic_noise(self, z_loc, factor=1.0, tolerance=1e-6, max_iter=1000):
         """factor * M^{1/2} z on sharded blob vectors by preconditioned Lanczos: the operator is P^T M P with
         the block-diagonal P of the local bodies (multi_bodies.py:591-615) and the result is mapped back with

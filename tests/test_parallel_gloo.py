@@ -169,6 +169,9 @@ class _CpuRigidBackend:
                 lam_out.append(Minv @ (slip + K @ U)); U_out.append(U)
             return torch.from_numpy(np.concatenate(lam_out + U_out))
 
+        def M_inv_mult(self, w):
+            return torch.from_numpy(np.concatenate([Minv @ x for (Minv, _, _, _, _), x in zip(self.blocks, self._split(w.numpy()))]))
+
         def mobility_pc(self, w, mobility_mult):
             v = np.concatenate([Li.T @ x for (_, _, _, _, Li), x in zip(self.blocks, self._split(w.numpy()))])
             mv = mobility_mult(torch.from_numpy(v)).numpy().reshape(-1)
@@ -206,7 +209,17 @@ def _rigid_worker(rank, world, port, out):
         eU = float((U_loc - U1[sys_sh.b0:sys_sh.b1]).abs().max() / U1.abs().max())
         eL = float((lam_loc.reshape(-1) - lam1.reshape(-1)[3 * o:3 * (o + c)]).abs().max() / lam1.abs().max())
         eN = float((noise_loc - noise1[3 * o:3 * (o + c)]).abs().max() / noise1.abs().max())
-        out[rank] = (info, info1, abs(its - its1), eU, eL, abs(it_l - it1), eN)
+        # resistance problem: sharded against single process, and against a dense solve of the assembled system
+        vel = rng.standard_normal((nb, 6))
+        F_loc, lamr_loc, its_r, info_r = sys_sh.solve_resistance(sys_sh.local_slice(vel), tolerance=1e-10)
+        F1, lamr1, its_r1, info_r1 = one.solve_resistance(torch.from_numpy(vel.reshape(-1)), tolerance=1e-10)
+        r_all = one.r_full.numpy().reshape(-1, 3)
+        Mdense = np.stack([oracle.mobility_product("UF", "single_wall", r_all, e, eta, a) for e in np.eye(r_all.size)], axis=1)
+        KU = _CpuRigidBackend.K_matrix_vector_prod(one.bodies, torch.from_numpy(vel.reshape(-1)), r_vectors=one.r_full)
+        lam_dense = np.linalg.solve(Mdense, KU.numpy().reshape(-1))
+        eF = float((F_loc - F1[sys_sh.b0:sys_sh.b1]).abs().max() / F1.abs().max())
+        eD = float(np.abs(lamr1.numpy().reshape(-1) - lam_dense).max() / np.abs(lam_dense).max())
+        out[rank] = (info, info1, abs(its - its1), eU, eL, abs(it_l - it1), eN, info_r, info_r1, abs(its_r - its_r1), eF, eD)
     finally:
         dist.destroy_process_group()
 
@@ -218,7 +231,8 @@ def test_sharded_rigid_system_world2():
     _spawn(_rigid_worker, world, out)
     assert len(out) == world
     for rank in range(world):
-        info, info1, dits, eU, eL, dl, eN = out[rank]
+        info, info1, dits, eU, eL, dl, eN, info_r, info_r1, dits_r, eF, eD = out[rank]
         assert info == 0 and info1 == 0 and dits <= 1
         assert eU < 1e-8 and eL < 1e-7
         assert dl <= 1 and eN < 1e-7
+        assert info_r == 0 and info_r1 == 0 and dits_r <= 1 and eF < 1e-7 and eD < 1e-7
