@@ -10,6 +10,8 @@ The reference selects its Mf implementation by string:
 register() makes all three reach the B200 kernels without editing the reference:
   * every `<name>_b200` / `<name>_b200_fp32` function is attached to the reference's `mobility` module;
   * set_mobility_vector_prod is wrapped to accept 'b200', 'b200_no_wall', 'b200_fp32', 'b200_no_wall_fp32';
+  * set_mobility_blobs (the DENSE blob mobility of one body, multi_bodies.py:205-227, input-file key
+    `mobility_blobs_implementation`, read_input.py:65) is wrapped to accept 'b200' and 'b200_no_wall';
   * optionally (alias_pycuda=True) the `<name>_pycuda` attributes of the mobility module are pointed at the B200
     functions, so that code paths (2) and (3), which look the functions up under their PyCUDA names, run on the
     B200 path when the input file says `mobility_vector_prod_implementation  pycuda`.
@@ -26,6 +28,12 @@ IMPLEMENTATIONS = {
 }
 
 
+DENSE_IMPLEMENTATIONS = {
+    "b200": "single_wall_fluid_mobility_b200",
+    "b200_no_wall": "rotne_prager_tensor_b200",
+}
+
+
 def attach(mobility_module, alias_pycuda=False):
     """Add the *_b200 functions to the reference's mobility module (mobility/mobility.py)."""
     for name in _mb.__all__:
@@ -39,6 +47,16 @@ def attach(mobility_module, alias_pycuda=False):
 def register(multi_bodies_module, alias_pycuda=False):
     """Wrap multi_bodies.set_mobility_vector_prod so the new implementation strings resolve."""
     attach(multi_bodies_module.mb, alias_pycuda=alias_pycuda)
+    original_blobs = getattr(multi_bodies_module, "set_mobility_blobs", None)
+    if original_blobs is not None and not getattr(original_blobs, "_b200_wrapped", False):
+        @functools.wraps(original_blobs)
+        def set_mobility_blobs(implementation, *args, **kwargs):
+            if implementation in DENSE_IMPLEMENTATIONS:
+                return getattr(_mb, DENSE_IMPLEMENTATIONS[implementation])
+            return original_blobs(implementation, *args, **kwargs)
+
+        set_mobility_blobs._b200_wrapped = True
+        multi_bodies_module.set_mobility_blobs = set_mobility_blobs
     original = multi_bodies_module.set_mobility_vector_prod
     if getattr(original, "_b200_wrapped", False):
         return multi_bodies_module

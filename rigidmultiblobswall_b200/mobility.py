@@ -140,6 +140,42 @@ def mobility_radii_trans_times_force(r_vectors, force, eta, a, radius_blobs, fun
     return function(r_vectors, r_vectors, force, radius_blobs, radius_blobs, eta, *args, **kwargs)
 
 
+def dense_mobility(wall, r_vectors, eta, a):
+    """Dense (3N, 3N) translational blob mobility, the matrix whose product with a force vector mobility_product(UF,
+    wall, ...) computes (open boundaries): what the reference assembles in Python loops / C++ for the bodies'
+    preconditioner blocks and the dense schemes (mobility.py:967-1116 -> multi_bodies.set_mobility_blobs,
+    multi_bodies.py:205-227).  One CUDA launch (rmb_body_mobility_blocks with the whole cloud as a single body)."""
+    from . import rigid
+    if wall not in (SINGLE_WALL, NO_WALL):
+        raise ValueError("dense_mobility: wall must be SINGLE_WALL or NO_WALL")
+    host_in = not isinstance(r_vectors, torch.Tensor)
+    dev = _device(None if host_in else r_vectors.device)
+    n = (r_vectors.numel() if isinstance(r_vectors, torch.Tensor) else np.asarray(r_vectors).size) // 3
+    if n > 30000:
+        raise ValueError("dense_mobility: %d blobs would need a %.0f GB matrix; use the matrix-free product" %
+                         (n, 9e-9 * 8 * n * n))
+    with torch.cuda.device(dev):
+        r = _as_device_f64(r_vectors, 3 * n, dev)
+        M = torch.empty(3 * n, 3 * n, dtype=torch.float64, device=dev)
+        if n > 0:
+            off = torch.tensor([0, n], dtype=torch.int64, device=dev)
+            rigid._check(rigid._rlib().rmb_body_mobility_blocks(
+                1, off.data_ptr(), n, r.data_ptr(), float(eta), float(a), int(wall == SINGLE_WALL), M.data_ptr(),
+                torch.cuda.current_stream(dev).cuda_stream))
+    return M.cpu().numpy() if host_in else M
+
+
+def single_wall_fluid_mobility_b200(r_vectors, eta, a, *args, **kwargs):
+    """B200 drop-in for mobility.single_wall_fluid_mobility / _cpp (mobility/mobility.py:1015-1116): dense mobility
+    above a wall, heights clamped to z >= a and damped by B on both sides."""
+    return dense_mobility(SINGLE_WALL, r_vectors, eta, a)
+
+
+def rotne_prager_tensor_b200(r_vectors, eta, a, *args, **kwargs):
+    """B200 drop-in for mobility.rotne_prager_tensor / _cpp (mobility/mobility.py:960-1013): dense free-space RPY."""
+    return dense_mobility(NO_WALL, r_vectors, eta, a)
+
+
 def _length3(periodic_length):
     L = np.zeros(3) if periodic_length is None else np.asarray(
         periodic_length.cpu() if isinstance(periodic_length, torch.Tensor) else periodic_length, dtype=np.float64)
@@ -219,7 +255,8 @@ _TABLE = [
     ("free_surface_mobility_trans_times_force", UF, FREE_SURFACE, 0, ":1390; :533"),
 ]
 
-__all__ = ["mobility_product", "mobility_source_target", "mobility_radii_trans_times_force"]
+__all__ = ["mobility_product", "mobility_source_target", "mobility_radii_trans_times_force", "dense_mobility",
+           "single_wall_fluid_mobility_b200", "rotne_prager_tensor_b200"]
 for _stem, _b, _w, _fl, _ref in _TABLE:
     for _suffix, _prec in (("_b200", FP64), ("_b200_fp32", FP32)):
         _name = _stem + _suffix

@@ -89,10 +89,14 @@ def test_registration_into_a_reference_like_module():
         if implementation == "numba":
             return ref_mb.single_wall_mobility_trans_times_force_numba
     mod.set_mobility_vector_prod = set_mobility_vector_prod
+    mod.set_mobility_blobs = lambda implementation: "python-dense" if implementation == "python" else None
     integration.register(mod, alias_pycuda=True)
     integration.register(mod)          # idempotent
     assert mod.set_mobility_vector_prod("numba")() == "numba"
     assert mod.set_mobility_vector_prod("b200") is mb.single_wall_mobility_trans_times_force_b200
+    assert mod.set_mobility_blobs("python") == "python-dense"
+    assert mod.set_mobility_blobs("b200") is mb.single_wall_fluid_mobility_b200
+    assert mod.set_mobility_blobs("b200_no_wall") is mb.rotne_prager_tensor_b200
     assert mod.set_mobility_vector_prod("b200_no_wall_fp32") is mb.no_wall_mobility_trans_times_force_b200_fp32
     assert ref_mb.single_wall_mobility_rot_times_torque_b200 is mb.single_wall_mobility_rot_times_torque_b200
     assert ref_mb.single_wall_mobility_trans_times_torque_pycuda is mb.single_wall_mobility_trans_times_torque_b200

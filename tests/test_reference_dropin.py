@@ -31,6 +31,10 @@ def test_implementation_strings_resolve_in_the_reference_driver(multi_bodies):
     assert multi_bodies.set_mobility_vector_prod("b200") is mb.single_wall_mobility_trans_times_force_b200
     assert multi_bodies.set_mobility_vector_prod("b200_no_wall") is mb.no_wall_mobility_trans_times_force_b200
     assert multi_bodies.set_mobility_vector_prod("b200_fp32") is mb.single_wall_mobility_trans_times_force_b200_fp32
+    # dense blob mobility of one body (mobility_blobs_implementation, multi_bodies.py:205-227)
+    assert multi_bodies.set_mobility_blobs("python") is multi_bodies.mb.single_wall_fluid_mobility
+    assert multi_bodies.set_mobility_blobs("b200") is mb.single_wall_fluid_mobility_b200
+    assert multi_bodies.set_mobility_blobs("b200_no_wall") is mb.rotne_prager_tensor_b200
     # the functions are reachable under the reference's own module, next to their numba twins
     for name in dir(multi_bodies.mb):
         if name.endswith("_numba") and name.startswith(("single_wall_mobility", "no_wall_mobility", "in_plane_mobility")) \

@@ -104,19 +104,3 @@ def test_prescribed_kinematics(gold):
     assert info == 0 and abs(its - int(g["gmres_iterations"][0])) <= 1
     assert relerr(vel, g["velocity"]) < 1e-8 and relerr(lam, g["lambda"]) < 1e-8
     assert relerr(rigid.K_matrix_T_vector_prod(bodies, lam, r_vectors=r).reshape(-1, 6), g["force"]) < 1e-8
-
-
-def test_sharded_resistance_single_rank(gold, setup):
-    """parallel.ShardedRigidSystem.solve_resistance on one rank against the reference's dense answer (the world-2
-    plumbing is covered on CPU by tests/test_parallel_gloo.py)"""
-    from rigidmultiblobswall_b200 import parallel
-    rg, g = gold
-    _, _, _, eta, a = setup
-    system = parallel.ShardedRigidSystem(rg["struct/boomerang_N_15"], rg["rigid/location"], rg["rigid/quaternion"],
-                                         eta, a, group=False)
-    slip = torch.from_numpy(g["slip"]).cuda().reshape(-1)
-    force, lam, its, info = system.solve_resistance(system.local_slice(g["velocity"].reshape(12, 6)), tolerance=1e-10,
-                                                    slip_loc=slip)
-    assert info == 0 and tuple(force.shape) == (12, 6)
-    assert relerr(lam, g["resistance/slip/force_blobs"]) < 1e-8
-    assert relerr(force, g["resistance/slip/force"]) < 1e-8

@@ -5,7 +5,7 @@
 #   gpurun --timeout 1500 -- 'bash tools/gpu_round2_start.sh r02a'
 mkdir -p gpurun_out
 T=${1:-r02a}
-echo "== new rigid tests"; timeout 120 python -m pytest tests/test_zz_schemes_gpu.py tests/test_zz_invariants.py -m gpu -q 2>&1 | tail -3
+echo "== new rigid tests"; timeout 120 python -m pytest tests/test_zzz_invariants_more.py tests/test_zzz_schemes_more_gpu.py -m gpu -q 2>&1 | tail -3
 echo "== pytest gpu"; timeout 1200 python -m pytest tests -m gpu -q > gpurun_out/${T}_pytest_gpu.log 2>&1; echo "rc=$?"; tail -2 gpurun_out/${T}_pytest_gpu.log
 echo "== smoke"; timeout 300 python __graft_entry__.py smoke > gpurun_out/${T}_smoke.log 2>&1; echo "rc=$?"; tail -3 gpurun_out/${T}_smoke.log
 echo "== bench"; timeout 900 python bench.py > gpurun_out/${T}_bench_1gpu.json 2> gpurun_out/${T}_bench.err; echo "rc=$?"; cut -c1-900 gpurun_out/${T}_bench_1gpu.json
