@@ -5,6 +5,7 @@ gmres    -- restarted, right-preconditioned GMRES; same contract as the
             scipy.sparse.linalg.gmres with A' = A P^-1 and returns x = P^-1 y.
 lanczos  -- stochastic_forcing.stochastic_forcing_lanczos
             (stochastic_forcing/stochastic_forcing.py:112-264): factor * M^{1/2} z.
+stochastic_forcing_eig / _eig_symm / _cholesky -- the reference's dense variants (:7-110) on torch tensors.
 
 The Krylov basis, all matvecs and all dot products stay on the GPU; only the
 (restart+1)-sized Hessenberg / tridiagonal data are handled on the host.  With
@@ -170,3 +171,33 @@ def lanczos(factor=1.0, tolerance=1e-6, max_iter=1000, dim=None, mobility_mult=N
         coef_old = coef
     noise = V[:len(coef_old)].T @ torch.from_numpy(coef_old).to(dev)
     return (noise if L_mult is None else L_mult(noise).reshape(-1)), max_iter
+
+
+# ---- dense M^{1/2} z (stochastic_forcing/stochastic_forcing.py:7-110): for the small systems whose dense mobility
+# ---- mobility.single_wall_fluid_mobility_b200 / rotne_prager_tensor_b200 assemble; same names, arguments and
+# ---- conventions as the reference, on torch tensors (plain library calls: eigh / cholesky)
+def _noise_vector(mobility, z, generator):
+    M = torch.as_tensor(mobility, dtype=torch.float64)
+    if z is None:
+        z = torch.randn(M.shape[0], dtype=torch.float64, device=M.device, generator=generator)
+    return M, torch.as_tensor(z, dtype=torch.float64).to(M.device).reshape(-1)
+
+
+def stochastic_forcing_eig(mobility, factor=1.0, z=None, generator=None):
+    """factor * V S^{1/2} z with M = V S V^T; negative eigenvalues count as 0 (stochastic_forcing.py:7-37)."""
+    M, z = _noise_vector(mobility, z, generator)
+    w, V = torch.linalg.eigh(M)
+    return factor * (V @ (torch.sqrt(torch.clamp(w, min=0.0)) * z))
+
+
+def stochastic_forcing_eig_symm(mobility, factor=1.0, z=None, generator=None):
+    """factor * V S^{1/2} V^T z, the symmetric square root (stochastic_forcing.py:40-73)."""
+    M, z = _noise_vector(mobility, z, generator)
+    w, V = torch.linalg.eigh(M)
+    return factor * (V @ (torch.sqrt(torch.clamp(w, min=0.0)) * (V.T @ z)))
+
+
+def stochastic_forcing_cholesky(mobility, factor=1.0, z=None, generator=None):
+    """factor * L z with M = L L^T (stochastic_forcing.py:77-110); M must be positive definite."""
+    M, z = _noise_vector(mobility, z, generator)
+    return factor * (torch.linalg.cholesky(M) @ z)

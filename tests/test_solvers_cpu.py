@@ -99,3 +99,39 @@ def test_lanczos_exact_on_diagonal_and_with_L_mult():
     assert torch.allclose(noise2, 3 * noise, atol=1e-10)
     zero, it0 = solvers.lanczos(factor=0.0, dim=10, z=z)
     assert it0 == 0 and float(zero.abs().sum()) == 0
+
+
+def test_dense_noise_functions_follow_the_reference():
+    """stochastic_forcing_{eig, eig_symm, cholesky} (stochastic_forcing.py:7-110) on the reference's own dense
+    single-wall mobility (tests/golden/dense_golden.npz); compared with the reference functions themselves when the
+    checkout is present, and always through their defining property  noise = factor * S z  with  S S^T = M."""
+    g = np.load(os.path.join(HERE, "golden", "dense_golden.npz"))
+    M = g["single_wall"]
+    rng = np.random.default_rng(8)
+    z = rng.standard_normal(M.shape[0])
+    Mt, zt = torch.from_numpy(M), torch.from_numpy(z)
+    eye = torch.eye(M.shape[0], dtype=torch.float64)
+    for fn in (solvers.stochastic_forcing_eig, solvers.stochastic_forcing_eig_symm, solvers.stochastic_forcing_cholesky):
+        S = torch.stack([fn(Mt, 1.0, eye[:, c]) for c in range(M.shape[0])], dim=1)       # the square-root factor
+        assert np.linalg.norm((S @ S.T).numpy() - M) < 1e-12 * np.linalg.norm(M)
+        assert torch.allclose(fn(Mt, 1.7, zt), 1.7 * (S @ zt), rtol=1e-12, atol=0)
+        w = fn(Mt, 0.5, None, generator=torch.Generator().manual_seed(1))
+        assert w.shape == (M.shape[0],) and torch.equal(w, fn(Mt, 0.5, None, generator=torch.Generator().manual_seed(1)))
+    Ssym = torch.stack([solvers.stochastic_forcing_eig_symm(Mt, 1.0, eye[:, c]) for c in range(M.shape[0])], dim=1)
+    assert torch.allclose(Ssym, Ssym.T, rtol=0, atol=1e-14)
+    ref_dir = "/root/reference/stochastic_forcing"
+    if os.path.exists(os.path.join(ref_dir, "stochastic_forcing.py")):
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("ref_stochastic_forcing", os.path.join(ref_dir, "stochastic_forcing.py"))
+        ref = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(ref)
+        # symmetric root and Cholesky factor are unique; the plain eig form depends on eigenvector signs, so it is
+        # compared through its covariance above only
+        assert np.allclose(solvers.stochastic_forcing_eig_symm(Mt, 1.3, zt).numpy(), ref.stochastic_forcing_eig_symm(M, 1.3, z),
+                           rtol=1e-10, atol=1e-14)
+        assert np.allclose(solvers.stochastic_forcing_cholesky(Mt, 1.3, zt).numpy(), ref.stochastic_forcing_cholesky(M, 1.3, z),
+                           rtol=1e-10, atol=1e-14)
+    # a singular mobility (eigenvalue 0) is legal for the eig forms, as in the reference
+    sing = torch.diag(torch.tensor([2.0, 0.0, 0.5], dtype=torch.float64))
+    assert torch.allclose(solvers.stochastic_forcing_eig_symm(sing, 1.0, torch.ones(3, dtype=torch.float64)),
+                          torch.tensor([2.0 ** 0.5, 0.0, 0.5 ** 0.5], dtype=torch.float64))
