@@ -62,6 +62,44 @@ def make_c2(n_bodies=1000, seed=77):
     return g["struct/boomerang_N_15"], loc, quat, FT, 0.25, 1.0, 1e-8
 
 
+def make_c3(n=100000, seed=3):
+    """BASELINE config 3: single-blob rollers above the wall, pseudo-periodic in xy, in-plane packing
+    fraction 0.4, heights in [a, 4.5a); a, eta of multi_bodies/examples/Mobility_Prod_Timing/Multiblob.inputfile:17-30."""
+    rng = np.random.default_rng(seed)
+    a, eta = 1.0155, 0.957e-3
+    Lxy = np.sqrt(np.pi * a * a * n / 0.4)
+    L = np.array([Lxy, Lxy, 0.0])
+    r = np.stack([Lxy * rng.random(n), Lxy * rng.random(n), a + 3.5 * a * rng.random(n)], axis=1)
+    return r, rng.standard_normal((n, 3)), rng.standard_normal((n, 3)), a, eta, L
+
+
+def make_c5(n_bodies=10000, seed=55):
+    """BASELINE config 5: shell_N_162 spheres (blob radius 0.26201755) on a square grid with spacing 3.0
+    at z in [1.5, 2.5), random unit quaternions, random force-torque, eta = 1, kT = 0.0041, dt = 0.01.
+    Returns (shell, a, eta, kT, dt, loc, quat, FT, z) -- the same arrays on every rank."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "rigid_golden.npz"))
+    shell = g["struct/shell_N_162"]
+    a = float(g["struct/shell_N_162_radius"][0])
+    rng = np.random.default_rng(seed)
+    side = int(np.ceil(np.sqrt(n_bodies)))
+    k = np.arange(n_bodies)
+    loc = np.stack([3.0 * (k % side), 3.0 * (k // side), 1.5 + rng.random(n_bodies)], axis=1)
+    quat = rng.standard_normal((n_bodies, 4))
+    quat /= np.linalg.norm(quat, axis=1)[:, None]
+    FT = rng.standard_normal((n_bodies, 6))
+    z = rng.standard_normal(3 * n_bodies * len(shell))
+    return shell, a, 1.0, 0.0041, 0.01, loc, quat, FT, z
+
+
+def make_dense_cloud(n, seed=4321):
+    """The C1 cloud of mobility/test_blobs.py:30-34 (N = 1000 in a 5a box: ~16 % overlapping pairs, ~20 % of the
+    blobs below z = a) scaled to n blobs at the SAME number density: box side 5a (n/1000)^(1/3), z from 0."""
+    rng = np.random.default_rng(seed)
+    a, eta = 0.13, 7.0
+    side = 5.0 * a * (n / 1000.0) ** (1.0 / 3.0)
+    return side * rng.random((n, 3)), rng.standard_normal((n, 3)), a, eta
+
+
 def gmres_mobility_solve(n_bodies=1000, repeats=3):
     """Secondary metric: wall seconds of the config-2 mobility solve (preconditioner build + GMRES), device
     resident, timed with CUDA events after one warm-up solve."""
