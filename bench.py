@@ -302,7 +302,7 @@ def run_b200(args):
         f_t = torch.from_numpy(f_host).to(dev, non_blocking=True)
         acc_e2e[0] = mb.symmetric_partial(r_t, f_t, eta, a, rank=rank, world=world, acc=acc_e2e[0])
         dist.all_reduce(acc_e2e[0])
-        return mb.symmetric_finish(n, acc_e2e[0], eta, a, targets=(off, cnt)).cpu().numpy()
+        return mb.symmetric_finish(r_t, f_t, acc_e2e[0], eta, a, targets=(off, cnt)).cpu().numpy()
 
     e2e_step()
     ms_e2e = timed(e2e_step, args.steps)

@@ -64,6 +64,8 @@ extern "C" {
                              flag the symmetric kernel is still chosen for eligible calls with
                              n_sources >= RMB_SYMMETRIC_MIN_N */
 #define RMB_DETERMINISTIC 8 /* never use the pair-symmetric kernel: one thread per target, fixed summation order */
+#define RMB_NO_FAR_BOXES 16 /* pseudo-periodic pair-symmetric kernels: test every image box for overlapping pairs, also
+                              when L >= 4a guarantees that only the central box can hold one (debug / A-B check) */
 #define RMB_SYMMETRIC_MIN_N 16384
 
 /* error codes */
@@ -122,18 +124,20 @@ int rmb_mobility_product(int block, int wall, int precision, int flags,
  *                            acc: device, rmb_symmetric_acc_len(n) doubles
  *   [sum acc over the ranks, e.g. ncclAllReduce]
  *   rmb_symmetric_finish()   out = B (acc + self term) / (8 pi eta a^k) for targets [target_offset, +n_targets);
- *                            same block, wall, a, L and workspace as the partial call (the workspace holds the packed
- *                            records and the damping)
+ *                            same block, wall, a, r, vec_a, vec_b as the partial call.  It reads ONLY its arguments
+ *                            (the height clamp, the damping B and B * v are recomputed per target): nothing is
+ *                            carried over from the partial call, whose workspace is pure scratch and may be reused
+ *                            by any other product in between.
  * rank = 0, world = 1 is what rmb_mobility_product(block, wall, RMB_FP64, RMB_SYMMETRIC, ...) does.
- * workspace: >= rmb_workspace_bytes(block, RMB_FP64, n, n, L).
+ * workspace (partial only): >= rmb_workspace_bytes(block, RMB_FP64, n, n, L).
  */
 size_t rmb_symmetric_acc_len(long n);
 int rmb_symmetric_partial(int block, int wall, int flags, long n, int rank, int world, const double *r,
                           const double *vec_a, const double *vec_b, double eta, double a, const double *L, double *acc, void *workspace,
                           size_t workspace_bytes, void *stream);
-int rmb_symmetric_finish(int block, int wall, int flags, long n, long target_offset, long n_targets, const double *acc,
-                         double eta, double a, const double *L, double *out, void *workspace,
-                         size_t workspace_bytes, void *stream);
+int rmb_symmetric_finish(int block, int wall, int flags, long n, long target_offset, long n_targets, const double *r,
+                         const double *vec_a, const double *vec_b, const double *acc, double eta, double a, double *out,
+                         void *stream);
 
 /*
  * Source-target UF product with per-blob radii: the flow at n_targets blobs

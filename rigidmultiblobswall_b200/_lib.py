@@ -10,7 +10,7 @@ from . import _build
 UF, UT, WF, WT, UF_UT = 0, 1, 2, 3, 4
 NO_WALL, SINGLE_WALL, FREE_SURFACE = 0, 1, 2
 FP64, FP32 = 0, 1
-IN_PLANE, NO_TMA, SYMMETRIC, DETERMINISTIC = 1, 2, 4, 8
+IN_PLANE, NO_TMA, SYMMETRIC, DETERMINISTIC, NO_FAR_BOXES = 1, 2, 4, 8, 16
 
 _lib = None
 
@@ -56,9 +56,8 @@ def load():
                                           c_dp, c_dp, ctypes.c_double, ctypes.c_double, ctypes.POINTER(ctypes.c_double),
                                           c_dp, c_dp, ctypes.c_size_t, c_dp]
     lib.rmb_symmetric_finish.restype = ctypes.c_int
-    lib.rmb_symmetric_finish.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_long, ctypes.c_long, ctypes.c_long, c_dp,
-                                         ctypes.c_double, ctypes.c_double, ctypes.POINTER(ctypes.c_double),
-                                         c_dp, c_dp, ctypes.c_size_t, c_dp]
+    lib.rmb_symmetric_finish.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_long, ctypes.c_long, ctypes.c_long,
+                                         c_dp, c_dp, c_dp, c_dp, ctypes.c_double, ctypes.c_double, c_dp, c_dp]
     lib.rmb_fma_peak.restype = ctypes.c_int
     lib.rmb_fma_peak.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double),
                                  ctypes.POINTER(ctypes.c_double)]

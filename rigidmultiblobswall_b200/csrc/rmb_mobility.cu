@@ -49,6 +49,9 @@ namespace {
 #ifndef RMB_SYM_UNROLL
 #define RMB_SYM_UNROLL 1  // rotation-loop unroll of the pair-symmetric kernel
 #endif
+#ifndef RMB_SYM_PER_UNROLL
+#define RMB_SYM_PER_UNROLL 2  // non-central image boxes of the pair-symmetric pseudo-periodic kernels (PER == 2)
+#endif
 #ifndef RMB_SYM_NT
 #define RMB_SYM_NT 1      // blobs per lane of the pair-symmetric kernel (1 or 2; TILE must be a multiple of 128 NT).
                           // Measured at N = 400k: 334.6 (1) vs 336.8 (2) G pairs/s, and 270 vs 252 at N = 20k
@@ -59,14 +62,20 @@ namespace {
 #ifndef RMB_SYM_MINB
 #define RMB_SYM_MINB(BLOCK) (((BLOCK) == UF || (BLOCK) == WF || (BLOCK) == WT) ? 5 : 1)
 #endif
-// A launch of the pair-symmetric kernel (a rank's share of the triangular rows) is split over blockIdx.y until it
-// has RMB_SYM_WAVES waves of RMB_SYM_RESIDENT CTAs per SM.  Measured (tools/time_rank_share.py, tools/tune.sh):
-// 10 -> 24 waves: one rank's eighth of N = 1M 383.5 -> 375.1 ms (ideal 369.4), N = 100k +4 %, N = 50k +6 %.
+// A launch of the pair-symmetric kernel (a rank's share of the triangular rows) is cut into equal-size items of
+// `chunk` tiles x one row group (sym_schedule.cuh): chunk is chosen so that each of the RMB_SYM_RESIDENT CTA slots
+// per SM gets >= RMB_SYM_ITEMS items, within [RMB_SYM_CHUNK_MIN, RMB_SYM_CHUNK_MAX] tiles.
 #ifndef RMB_SYM_RESIDENT
 #define RMB_SYM_RESIDENT 5
 #endif
-#ifndef RMB_SYM_WAVES
-#define RMB_SYM_WAVES 24
+#ifndef RMB_SYM_ITEMS
+#define RMB_SYM_ITEMS 128
+#endif
+#ifndef RMB_SYM_CHUNK_MIN
+#define RMB_SYM_CHUNK_MIN 4
+#endif
+#ifndef RMB_SYM_CHUNK_MAX
+#define RMB_SYM_CHUNK_MAX 16
 #endif
 #ifndef RMB_WAVES
 #define RMB_WAVES 10
@@ -346,8 +355,9 @@ struct SymArgs {
   const double* src;              // n_tiles * TILE records of W words {x, y, z, v[3 NV], pad}; padding = zero vectors (see TAIL)
   double* acc;                    // [n_tiles * TILE][3], zeroed before the launch
   long n;                         // real blobs; records [n, n_tiles * TILE) are zero-force padding
-  int n_tiles, n_split;
-  int row_first, row_stride;      // row groups handled by this launch: row_first + blockIdx.x * row_stride
+  int n_tiles;
+  int rows, chunk;                // row groups of this launch; tiles per work item (sym_item)
+  int row_first, row_stride;      // row groups handled by this launch: row_first + k * row_stride, k < rows
   UfCtx<double> K;
   // PER instantiations only (pseudo-periodic in x and/or y; records then hold unscaled positions)
   Periodic<double> P;
@@ -405,7 +415,7 @@ __device__ __forceinline__ void sym_pair(double rx, double ry, double rz, double
   }
 }
 
-template <bool PER>
+template <int PER>
 __device__ __forceinline__ void sym_geometry(const SymArgs& A, double xi, double yi, double hi, const double* w,
                                              double& rx, double& ry, double& rz, double& hj)
 {
@@ -421,7 +431,11 @@ __device__ __forceinline__ void sym_geometry(const SymArgs& A, double xi, double
   rz = hi - hj;
 }
 
-template <int BLOCK, int NT, int K0, int NK, bool TAIL, bool WALL, bool PER>
+// PER: 0 open boundaries; 1 pseudo-periodic, every image box tested for overlapping pairs; 2 pseudo-periodic with
+// L >= 4a in every periodic direction (host-checked): after the minimum-image wrap |r_d| <= L_d / 2, so a pair in a
+// non-central box is at least L_d / 2 >= 2a apart -- only the central box (first in SymArgs::box) can hold an
+// overlapping pair; the other boxes run the far-field code with no vote, no select and no branch.
+template <int BLOCK, int NT, int K0, int NK, bool TAIL, bool WALL, int PER>
 __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int lane,
                                           SymLane<NT, SymRec<BLOCK>::NV>& L, const SymArgs& A,
                                           double* __restrict__ acc_j, long i0, long j0)
@@ -450,7 +464,7 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
         const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
         const bool any_near = __any_sync(0xffffffffu, lt4(r2));
         sym_pair<BLOCK, WALL, true>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
-      } else {
+      } else if (PER == 1) {
         const T Rz = hi + hj, rz2 = rz * rz;
 #pragma unroll 1
         for (int b = 0; b < A.box.n; b++) {
@@ -458,6 +472,20 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
           const T r2 = RMB_FMA(by, by, RMB_FMA(bx, bx, rz2));
           const bool any_near = __any_sync(0xffffffffu, lt4(r2));
           sym_pair<BLOCK, WALL, true>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
+        }
+      } else {
+        const T Rz = hi + hj, rz2 = rz * rz;
+        {
+          const T r2 = RMB_FMA(ry, ry, RMB_FMA(rx, rx, rz2));
+          const bool any_near = __any_sync(0xffffffffu, lt4(r2));
+          sym_pair<BLOCK, WALL, true>(rx, ry, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
+        }
+        constexpr int PU = RMB_SYM_PER_UNROLL;
+#pragma unroll PU
+        for (int b = 1; b < A.box.n; b++) {
+          const T bx = rx + A.box.s[b][0], by = ry + A.box.s[b][1];
+          const T r2 = RMB_FMA(by, by, RMB_FMA(bx, bx, rz2));
+          sym_pair<BLOCK, WALL, true>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, false, r2, L.u[k], aj);
         }
       }
     }
@@ -472,7 +500,8 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
 
 // Diagonal block (J == the block of blob k): ordered pairs (l, (l + s) & 31), s = 1..31, one direction.
 // PER: also s = 0, the blob's own images in the non-central boxes.
-template <int BLOCK, int NT, bool TAIL, bool WALL, bool PER>
+// (the diagonal block is 1 / n_blocks of the work: the generic box loop serves PER == 1 and PER == 2)
+template <int BLOCK, int NT, bool TAIL, bool WALL, int PER>
 __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lane, SymLane<NT, SymRec<BLOCK>::NV>& L, int k,
                                          const SymArgs& A, long i0)
 {
@@ -509,7 +538,7 @@ __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lan
   }
 }
 
-template <int BLOCK, bool TMA, int NT, bool WALL, bool PER>
+template <int BLOCK, bool TMA, int NT, bool WALL, int PER>
 __global__ void __launch_bounds__(TPB, RMB_SYM_MINB(BLOCK)) sym_kernel(const __grid_constant__ SymArgs A)
 {
   typedef double T;
@@ -522,8 +551,12 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB(BLOCK)) sym_kernel(const __g
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   // (broadcasting `warp` with __shfl_sync makes the block index provably uniform and removes the BRA.DIV / WARPSYNC
   // guards around the shuffles -- 125 -> 122 instructions per step -- but measured 3.6 % SLOWER: 338 -> 326 G pairs/s)
-  const int g = A.row_first + blockIdx.x * A.row_stride;   // row group of ROW blobs
-  const long I0 = ((long)g * (TPB / 32) + warp) * NT;      // this warp's first block of 32
+  // this CTA's work item: row group g of ROW blobs x the tiles [v0, v1) of its row [g * ROW / TILE, n_tiles)
+  const SymItem item = sym_item((int)blockIdx.x, (int)blockIdx.y, A.rows, A.row_first, A.row_stride, ROW, TILE,
+                                A.n_tiles, A.chunk);
+  if (!item.valid) return;
+  const long g = item.g;
+  const long I0 = (g * (TPB / 32) + warp) * NT;            // this warp's first block of 32
 
   constexpr int NV = SymRec<BLOCK>::NV;
   const T* srcw = A.src;
@@ -538,9 +571,7 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB(BLOCK)) sym_kernel(const __g
 #pragma unroll
     for (int c = 0; c < 3; c++) L.u[k][c] = 0.0;
   }
-  // this CTA's part of the row's tiles [g * ROW / TILE, n_tiles)
-  const SymRowPart part = sym_row_part(g, ROW, TILE, A.n_tiles, (int)blockIdx.y, A.n_split);
-  const int v0 = part.v0, v1 = part.v1;
+  const int v0 = item.v0, v1 = item.v1;
 
   if (TMA) {
     if (tid == 0) {
@@ -599,21 +630,30 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB(BLOCK)) sym_kernel(const __g
   }
 }
 
-// out = B (acc + self term) / (8 pi eta a) for the targets [tgt_off, tgt_off + n_tgt)
+// out = B (acc + self term) / (8 pi eta a^k) for the targets [tgt_off, tgt_off + n_tgt).  Reads the caller's own
+// arrays (positions, vectors), not the packed records of the partial step: the clamp, the damping B and B * v are
+// O(1) per target (mobility.py:52-84), so the finish step depends on nothing but its arguments.
 template <int BLOCK, bool WALL>
-__global__ void sym_finish_kernel(const SrcRec<double, SymRec<BLOCK>::NV>* __restrict__ src, const double* __restrict__ acc,
-                                  const double* __restrict__ damp, long tgt_off, long n_tgt, double norm, int in_plane,
-                                  double zscale, double* __restrict__ out)
+__global__ void sym_finish_kernel(const double* __restrict__ r, const double* __restrict__ va,
+                                  const double* __restrict__ vb, const double* __restrict__ acc, long tgt_off,
+                                  long n_tgt, double a, double norm, int in_plane, double* __restrict__ out)
 {
   const long li = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (li >= n_tgt) return;
   const long gi = tgt_off + li;
-  const SrcRec<double, SymRec<BLOCK>::NV>& me = src[gi];
-  double sv[6] = {me.v[0], me.v[1], me.v[2], 0.0, 0.0, 0.0};
-  if (SymRec<BLOCK>::NV == 2) { sv[3] = me.v[3]; sv[4] = me.v[4]; sv[5] = me.v[5]; }
+  const double inva = 1.0 / a;
+  double z = r[3 * gi + 2], B = 1.0;
+  if (WALL) {
+    B = (z < a) ? z / a : 1.0;
+    z = (z <= a) ? a : z;
+  }
+  double sv[6] = {B * va[3 * gi], B * va[3 * gi + 1], in_plane ? 0.0 : B * va[3 * gi + 2], 0.0, 0.0, 0.0};
+  if (SymRec<BLOCK>::NV == 2) {
+    sv[3] = B * vb[3 * gi] * inva; sv[4] = B * vb[3 * gi + 1] * inva; sv[5] = in_plane ? 0.0 : B * vb[3 * gi + 2] * inva;
+  }
   double dx = acc[3 * gi], dy = acc[3 * gi + 1], dz = acc[3 * gi + 2];
-  self_apply<double, BLOCK, WALL>(me.z * zscale, sv, dx, dy, dz);   // zscale: 1/a when the records are unscaled
-  const double sc = norm * damp[gi];
+  self_apply<double, BLOCK, WALL>(z * inva, sv, dx, dy, dz);
+  const double sc = norm * B;
   out[3 * li] = dx * sc;
   out[3 * li + 1] = dy * sc;
   out[3 * li + 2] = in_plane ? 0.0 : dz * sc;
@@ -761,7 +801,8 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
   cudaError_t e = cudaMemsetAsync(acc, 0, (size_t)n_pad * 3 * sizeof(double), c.stream);
   if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product: memset");
   SymArgs A;
-  A.src = reinterpret_cast<const double*>(c.ws); A.acc = acc; A.n = c.n_src; A.n_tiles = p.n_tiles; A.n_split = 1;
+  A.src = reinterpret_cast<const double*>(c.ws); A.acc = acc; A.n = c.n_src; A.n_tiles = p.n_tiles;
+  A.rows = 0; A.chunk = 1;
   A.row_first = row_first; A.row_stride = row_stride;
   A.K = make_uf_ctx<double>(0.0);
   A.P.nbox = p.n_boxes;
@@ -772,21 +813,41 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
   }
   A.inva = 1.0 / c.a;
   A.box = make_box_table<double>(A.P, 1.0 / c.a);
+  // the central box first (PER == 2 treats it apart); far-only non-central boxes need L >= 4a
+  bool far_boxes = per;
+  for (int d = 0; d < 2; d++)
+    if (A.P.per[d] && c.L[d] < 4.0 * c.a) far_boxes = false;
+  if (per && A.box.central != 0) {
+    for (int d = 0; d < 3; d++) {
+      const double t = A.box.s[0][d];
+      A.box.s[0][d] = A.box.s[A.box.central][d];
+      A.box.s[A.box.central][d] = t;
+    }
+    A.box.central = 0;
+  }
+  const int pm = per ? ((far_boxes && !(c.flags & RMB_NO_FAR_BOXES)) ? 2 : 1) : 0;
   const long rows_all = n_pad / (TPB * RMB_SYM_NT);
   const long rows = (rows_all - row_first + row_stride - 1) / row_stride;
   if (rows > 0) {
-    // rows are triangular (1 .. n_tiles tiles): split them over blockIdx.y until THIS launch (a rank's share of
-    // the rows) has at least RMB_SYM_WAVES waves of resident CTAs, so that the tail is short
-    const int split = sym_split_for(rows, (long)sm_count() * RMB_SYM_RESIDENT, RMB_SYM_WAVES, p.n_tiles);
-    A.n_split = split;
-    const dim3 grid((unsigned)rows, (unsigned)split);
+    // rows are triangular (1 .. n_tiles tiles): THIS launch (a rank's share of the rows) is cut into equal-size
+    // items of `chunk` tiles, one CTA each, rows paired long + short so that the grid is rectangular
     constexpr int NT = RMB_SYM_NT;
+    A.rows = (int)rows;
+    A.chunk = sym_chunk_for(rows, row_first, row_stride, TPB * NT, TILE, p.n_tiles, (long)sm_count() * RMB_SYM_RESIDENT,
+                            RMB_SYM_ITEMS, RMB_SYM_CHUNK_MIN, RMB_SYM_CHUNK_MAX);
+    const int gy = sym_grid_y(A.rows, row_first, row_stride, TPB * NT, TILE, p.n_tiles, A.chunk);
+    if (gy > 65535) return fail(RMB_E_ARG, "pair-symmetric product: too many chunks per row pair");
+    const dim3 grid((unsigned)((rows + 1) / 2), (unsigned)gy);
+#define RMB_SYM_LAUNCH_W(B, W)                                                              \
+    do {                                                                                   \
+      if (pm == 2) sym_kernel<B, true, NT, W, 2><<<grid, TPB, 0, c.stream>>>(A);            \
+      else if (pm == 1) sym_kernel<B, true, NT, W, 1><<<grid, TPB, 0, c.stream>>>(A);       \
+      else sym_kernel<B, true, NT, W, 0><<<grid, TPB, 0, c.stream>>>(A);                    \
+    } while (0)
 #define RMB_SYM_LAUNCH(B)                                                                  \
     do {                                                                                   \
-      if (wall && per) sym_kernel<B, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);   \
-      else if (wall) sym_kernel<B, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);    \
-      else if (per) sym_kernel<B, true, NT, false, true><<<grid, TPB, 0, c.stream>>>(A);     \
-      else sym_kernel<B, true, NT, false, false><<<grid, TPB, 0, c.stream>>>(A);             \
+      if (wall) RMB_SYM_LAUNCH_W(B, true);                                                 \
+      else RMB_SYM_LAUNCH_W(B, false);                                                     \
     } while (0)
     if (c.block == RMB_UF_UT) {
       RMB_SYM_LAUNCH(UF_UT);
@@ -795,13 +856,13 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
     } else if (c.block == RMB_UT || (c.block == RMB_WF && !wall)) {   // free space: WF is the same function as UT
       RMB_SYM_LAUNCH(UT);
     } else if (c.block == RMB_WF) {
-      if (per) sym_kernel<WF, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
-      else sym_kernel<WF, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
-    } else if (per && wall) sym_kernel<UF, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
-    else if (per) sym_kernel<UF, true, NT, false, true><<<grid, TPB, 0, c.stream>>>(A);
-    else if (!wall) sym_kernel<UF, true, NT, false, false><<<grid, TPB, 0, c.stream>>>(A);
-    else if (c.flags & RMB_NO_TMA) sym_kernel<UF, false, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
-    else sym_kernel<UF, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
+      RMB_SYM_LAUNCH_W(WF, true);
+    } else if (pm == 0 && wall && (c.flags & RMB_NO_TMA)) {
+      sym_kernel<UF, false, NT, true, 0><<<grid, TPB, 0, c.stream>>>(A);
+    } else {
+      RMB_SYM_LAUNCH(UF);
+    }
+#undef RMB_SYM_LAUNCH_W
 #undef RMB_SYM_LAUNCH
   }
   e = cudaGetLastError();
@@ -809,17 +870,14 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
   return 0;
 }
 
-// Step 2: out = B (acc + self term) / (8 pi eta a) for a target range (records and damping from step 1's workspace).
+// Step 2: out = B (acc + self term) / (8 pi eta a^k) for a target range, from the caller's arrays and acc only.
 int sym_finish(const Call& c, const double* acc)
 {
-  const Plan& p = c.plan;
-  const double* damp = reinterpret_cast<const double*>(c.ws + p.off_damp);
   const unsigned nb = (unsigned)((c.n_tgt + 127) / 128);
   const int in_plane = (c.flags & RMB_IN_PLANE) ? 1 : 0;
-  const double zscale = (c.L[0] > 0 || c.L[1] > 0) ? 1.0 / c.a : 1.0;
   const double norm = block_norm(c.block, c.eta, c.a);
 #define RMB_SYM_FINISH(B, W) sym_finish_kernel<B, W><<<nb, 128, 0, c.stream>>>( \
-      reinterpret_cast<const SrcRec<double, SymRec<B>::NV>*>(c.ws), acc, damp, c.tgt_off, c.n_tgt, norm, in_plane, zscale, c.out)
+      c.r, c.va, c.vb, acc, c.tgt_off, c.n_tgt, c.a, norm, in_plane, c.out)
   const bool wall = c.wall == RMB_SINGLE_WALL;
   if (c.block == RMB_UF_UT) { if (wall) RMB_SYM_FINISH(UF_UT, true); else RMB_SYM_FINISH(UF_UT, false); }
   else if (c.block == RMB_UT) { if (wall) RMB_SYM_FINISH(UT, true); else RMB_SYM_FINISH(UT, false); }
@@ -979,18 +1037,26 @@ int rmb_symmetric_partial(int block, int wall, int flags, long n, int rank, int 
   return rc != 0 ? rc : sym_partial(c, acc, rank, world);
 }
 
-int rmb_symmetric_finish(int block, int wall, int flags, long n, long target_offset, long n_targets, const double* acc,
-                         double eta, double a, const double* L, double* out, void* workspace, size_t workspace_bytes,
+int rmb_symmetric_finish(int block, int wall, int flags, long n, long target_offset, long n_targets, const double* r,
+                         const double* vec_a, const double* vec_b, const double* acc, double eta, double a, double* out,
                          void* stream)
 {
+  if (n <= 0) return fail(RMB_E_ARG, "n must be positive");
+  if (block < RMB_UF || block > RMB_UF_UT) return fail(RMB_E_ARG, "block must be RMB_UF..RMB_UF_UT");
+  if (wall != RMB_SINGLE_WALL && wall != RMB_NO_WALL)
+    return fail(RMB_E_ARG, "the pair-symmetric product exists for RMB_SINGLE_WALL and RMB_NO_WALL");
   if (target_offset < 0 || n_targets < 0 || target_offset + n_targets > n)
     return fail(RMB_E_ARG, "target range must lie inside [0, n)");
   if (n_targets == 0) return 0;
-  if (!acc || !out) return fail(RMB_E_ARG, "null device pointer");
+  if (!r || !vec_a || !acc || !out) return fail(RMB_E_ARG, "null device pointer");
+  if (block == RMB_UF_UT && !vec_b) return fail(RMB_E_ARG, "RMB_UF_UT needs vec_b (torque)");
+  if (!(a > 0) || !(eta > 0)) return fail(RMB_E_ARG, "a and eta must be positive");
   Call c;
-  const int rc = sym_call(c, block, wall, flags, n, nullptr, nullptr, nullptr, eta, a, L, workspace, workspace_bytes, stream);
-  if (rc != 0) return rc;
-  c.tgt_off = target_offset; c.n_tgt = n_targets; c.out = out;
+  c.block = block; c.wall = wall; c.precision = RMB_FP64; c.flags = flags;
+  c.n_tgt = n_targets; c.n_src = n; c.tgt_off = target_offset;
+  c.r = r; c.va = vec_a; c.vb = vec_b; c.eta = eta; c.a = a;
+  for (int d = 0; d < 3; d++) c.L[d] = 0.0;
+  c.out = out; c.ws = nullptr; c.stream = static_cast<cudaStream_t>(stream);
   return sym_finish(c, acc);
 }
 

@@ -29,7 +29,8 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import (DETERMINISTIC, FP32, FP64, FREE_SURFACE, IN_PLANE, NO_TMA, NO_WALL, SINGLE_WALL, SYMMETRIC, UF,  # noqa: F401
+from ._lib import (DETERMINISTIC, FP32, FP64, FREE_SURFACE, IN_PLANE, NO_FAR_BOXES, NO_TMA, NO_WALL, SINGLE_WALL,  # noqa: F401
+                   SYMMETRIC, UF,
                    UF_UT, UT, WF, WT)
 
 _workspaces = {}
@@ -205,22 +206,24 @@ def symmetric_partial(r_vectors, force, eta, a, rank=0, world=1, acc=None, flags
     return acc
 
 
-def symmetric_finish(n, acc, eta, a, targets=None, out=None, flags=0, wall=SINGLE_WALL, periodic_length=None,
-                     block=UF):
+def symmetric_finish(r_vectors, vec, acc, eta, a, targets=None, out=None, flags=0, wall=SINGLE_WALL, block=UF,
+                     vec_b=None):
     """Step 2 (rmb_symmetric_finish) after the ranks' acc have been summed: self term, normalisation, damping for
-    the target range.  Must follow symmetric_partial (same block, wall, a, periodic_length) on the same device and
-    stream: it reads that call's workspace."""
+    the target range, from the same r_vectors / vec (/ vec_b) the partial step was given.  Stateless: it reads its
+    arguments only, so other products may run between the two steps."""
     lib = _lib.load()
     dev = acc.device
+    n = (r_vectors.numel() if isinstance(r_vectors, torch.Tensor) else np.asarray(r_vectors).size) // 3
     off, cnt = (0, n) if targets is None else targets
     with torch.cuda.device(dev):
+        r = _as_device_f64(r_vectors, 3 * n, dev)
+        f = _as_device_f64(vec, 3 * n, dev)
+        vb = _as_device_f64(vec_b, 3 * n, dev) if block == UF_UT else None
         if out is None:
             out = torch.empty(3 * cnt, dtype=torch.float64, device=dev)
-        Lc = _length3(periodic_length)
-        ws = _workspace(lib.rmb_workspace_bytes(block, FP64, n, n, Lc), dev)
-        _lib.check(lib.rmb_symmetric_finish(block, wall, flags | default_flags, n, off, cnt, acc.data_ptr(), float(eta),
-                                            float(a), Lc, out.data_ptr(), ws.data_ptr(), ws.numel(),
-                                            torch.cuda.current_stream(dev).cuda_stream))
+        _lib.check(lib.rmb_symmetric_finish(block, wall, flags | default_flags, n, off, cnt, r.data_ptr(), f.data_ptr(),
+                                            vb.data_ptr() if vb is not None else None, acc.data_ptr(), float(eta),
+                                            float(a), out.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
     return out
 
 

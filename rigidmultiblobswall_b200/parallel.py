@@ -100,13 +100,12 @@ class ShardedMobility:
         full = self.vec.gather(vec_local)
         if not self.symmetric:
             return self._product(self.r, full, (self.offset, self.count))
-        n = self.r.numel() // 3
         self._acc = _mb.symmetric_partial(self.r, full, self.eta, self.a, rank=self.rank, world=self.world,
                                           acc=self._acc, wall=self.wall, periodic_length=self.L, block=self.block)
         if self.world > 1:
             dist.all_reduce(self._acc, group=self.group)
-        return _mb.symmetric_finish(n, self._acc, self.eta, self.a, targets=(self.offset, self.count),
-                                    wall=self.wall, periodic_length=self.L, block=self.block)
+        return _mb.symmetric_finish(self.r, full, self._acc, self.eta, self.a, targets=(self.offset, self.count),
+                                    wall=self.wall, block=self.block)
 
 
 def _global_norm(x, group):

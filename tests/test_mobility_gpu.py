@@ -260,8 +260,13 @@ def test_default_selection_and_deterministic_flag(mb):
     assert float(torch.linalg.norm(sym - det) / torch.linalg.norm(det)) < 1e-13
     world = 3
     acc = sum(mb.symmetric_partial(r, f, eta, a, rank=k, world=world).clone() for k in range(world))
-    mb.symmetric_partial(r, f, eta, a, rank=0, world=world)       # finish reads the records of the last partial
-    out = torch.cat([mb.symmetric_finish(n, acc, eta, a, targets=t) for t in ((0, 9000), (9000, 11000))])
+    # the finish step reads its arguments only: unrelated products on the same stream between the two steps
+    # (a bigger cloud, another block, a source-target call) must not change the result
+    r_big = torch.from_numpy(rng.random((n + 5000, 3)) + 1.0).cuda()
+    mb.mobility_product(mb.WT, mb.SINGLE_WALL, r_big, r_big, eta, a)
+    mb.mobility_source_target(mb.NO_WALL, r_big[:100], r, r_big[:100], torch.ones(100).cuda().double(),
+                              torch.ones(n).cuda().double(), eta)
+    out = torch.cat([mb.symmetric_finish(r, f, acc, eta, a, targets=t) for t in ((0, 9000), (9000, 11000))])
     assert float(torch.linalg.norm(out - det) / torch.linalg.norm(det)) < 1e-13
 
 
@@ -365,7 +370,7 @@ def test_symmetric_periodic_large_default_and_multi_rank(mb):
         world = 3
         acc = sum(mb.symmetric_partial(r, f, eta, a, rank=k, world=world, wall=w, periodic_length=L).clone()
                   for k in range(world))
-        out = torch.cat([mb.symmetric_finish(n, acc, eta, a, targets=t, wall=w, periodic_length=L)
+        out = torch.cat([mb.symmetric_finish(r, f, acc, eta, a, targets=t, wall=w)
                          for t in ((0, 9000), (9000, 11000))])
         assert float(torch.linalg.norm(out - det) / torch.linalg.norm(det)) < 1e-13
     import oracle
@@ -429,7 +434,7 @@ def test_symmetric_rotation_blocks_large_default_and_multi_rank(mb, blk):
         world = 3
         acc = sum(mb.symmetric_partial(r, v, eta, a, rank=k, world=world, block=b, periodic_length=L).clone()
                   for k in range(world))
-        out = torch.cat([mb.symmetric_finish(n, acc, eta, a, targets=t, block=b, periodic_length=L)
+        out = torch.cat([mb.symmetric_finish(r, v, acc, eta, a, targets=t, block=b)
                          for t in ((0, 9000), (9000, 11000))])
         assert float(torch.linalg.norm(out - det) / torch.linalg.norm(det)) < 1e-13
     nw = mb.mobility_product(b, mb.NO_WALL, r, v, eta, a, flags=mb.SYMMETRIC)
@@ -483,7 +488,7 @@ def test_symmetric_fused_large_default_and_multi_rank(mb):
         world = 3
         acc = sum(mb.symmetric_partial(r, f, eta, a, rank=k, world=world, block=mb.UF_UT, vec_b=t,
                                        periodic_length=L).clone() for k in range(world))
-        out = torch.cat([mb.symmetric_finish(n, acc, eta, a, targets=tg, block=mb.UF_UT, periodic_length=L)
+        out = torch.cat([mb.symmetric_finish(r, f, acc, eta, a, targets=tg, block=mb.UF_UT, vec_b=t)
                          for tg in ((0, 9000), (9000, 11000))])
         assert float(torch.linalg.norm(out - det) / torch.linalg.norm(det)) < 1e-13
 

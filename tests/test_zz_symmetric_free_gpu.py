@@ -81,6 +81,6 @@ def test_large_default_and_multi_rank(mb, blk):
         world = 3
         acc = sum(mb.symmetric_partial(r, v, eta, a, rank=k, world=world, block=b, wall=mb.NO_WALL, vec_b=t,
                                        periodic_length=L).clone() for k in range(world))
-        out = torch.cat([mb.symmetric_finish(n, acc, eta, a, targets=tg, block=b, wall=mb.NO_WALL, periodic_length=L)
+        out = torch.cat([mb.symmetric_finish(r, v, acc, eta, a, targets=tg, block=b, wall=mb.NO_WALL, vec_b=t)
                          for tg in ((0, 9000), (9000, 11000))])
         assert float(torch.linalg.norm(out - det) / torch.linalg.norm(det)) < 1e-13
