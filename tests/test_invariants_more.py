@@ -1,12 +1,12 @@
 """More invariants on both backends (CPU oracle in the `not gpu` suite, CUDA path in the `gpu` suite), same harness as
-tests/test_zz_invariants.py: the a -> 0 limit against Blake's point-force image system, the fused clamp + damping as
+tests/test_invariants.py: the a -> 0 limit against Blake's point-force image system, the fused clamp + damping as
 B M(r_eff) B also below the wall plane, and the columns of the product against the reference's DENSE matrices."""
 import os
 
 import numpy as np
 import pytest
 
-from test_zz_invariants import BLOCKS, dense, product  # noqa: F401  (product: the backend fixture)
+from test_invariants import BLOCKS, dense, product  # noqa: F401  (product: the backend fixture)
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 

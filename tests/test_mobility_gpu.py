@@ -416,7 +416,7 @@ def test_symmetric_rotation_blocks_ragged_vs_oracle(mb, n):
 @pytest.mark.parametrize("blk", ["UT", "WF", "WT"])
 def test_symmetric_rotation_blocks_large_default_and_multi_rank(mb, blk):
     """n >= RMB_SYMMETRIC_MIN_N: default = symmetric kernel, equal to the row kernel (RMB_DETERMINISTIC) and to the
-    multi-rank form (world = 3 on one device, sums added by hand); the no-wall twins: tests/test_zz_symmetric_free_gpu.py"""
+    multi-rank form (world = 3 on one device, sums added by hand); the no-wall twins: tests/test_symmetric_free_gpu.py"""
     from rigidmultiblobswall_b200 import _lib
     lib = _lib.load()
     rng = np.random.default_rng(41)

@@ -2,7 +2,7 @@
 preconditioner's apply, the mobility / resistance / body_mobility schemes and prescribed kinematics, with the three
 CUDA entry points they call (K, K^T, blob mobility) replaced by dense NumPy stand-ins and the CPU oracle.  Answers
 are the reference's own (tests/golden/{rigid,resistance,prescribed}_golden.npz).  The same functions run against the
-real kernels in tests/test_rigid_gpu.py and tests/test_zz_schemes_gpu.py."""
+real kernels in tests/test_rigid_gpu.py and tests/test_schemes_gpu.py."""
 import os
 
 import numpy as np

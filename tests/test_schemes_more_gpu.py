@@ -1,12 +1,12 @@
 """GPU tests of the sharded resistance solve on one rank and of the dense-mobility drop-ins
-(multi_bodies.set_mobility_blobs 'b200' / 'b200_no_wall'); fixtures shared with tests/test_zz_schemes_gpu.py."""
+(multi_bodies.set_mobility_blobs 'b200' / 'b200_no_wall'); fixtures shared with tests/test_schemes_gpu.py."""
 import os
 
 import numpy as np
 import pytest
 
 torch = pytest.importorskip("torch")
-from test_zz_schemes_gpu import gold, relerr, setup  # noqa: E402,F401
+from test_schemes_gpu import gold, relerr, setup  # noqa: E402,F401
 
 pytestmark = pytest.mark.gpu
 HERE = os.path.dirname(os.path.abspath(__file__))
