@@ -64,8 +64,6 @@ extern "C" {
                              flag the symmetric kernel is still chosen for eligible calls with
                              n_sources >= RMB_SYMMETRIC_MIN_N */
 #define RMB_DETERMINISTIC 8 /* never use the pair-symmetric kernel: one thread per target, fixed summation order */
-#define RMB_NO_FAR_BOXES 16 /* pseudo-periodic pair-symmetric kernels: test every image box for overlapping pairs, also
-                              when L >= 4a guarantees that only the central box can hold one (debug / A-B check) */
 #define RMB_SYMMETRIC_MIN_N 16384
 
 /* error codes */

@@ -10,7 +10,7 @@ from . import _build
 UF, UT, WF, WT, UF_UT = 0, 1, 2, 3, 4
 NO_WALL, SINGLE_WALL, FREE_SURFACE = 0, 1, 2
 FP64, FP32 = 0, 1
-IN_PLANE, NO_TMA, SYMMETRIC, DETERMINISTIC, NO_FAR_BOXES = 1, 2, 4, 8, 16
+IN_PLANE, NO_TMA, SYMMETRIC, DETERMINISTIC = 1, 2, 4, 8
 
 _lib = None
 

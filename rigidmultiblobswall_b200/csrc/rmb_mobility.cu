@@ -49,9 +49,6 @@ namespace {
 #ifndef RMB_SYM_UNROLL
 #define RMB_SYM_UNROLL 1  // rotation-loop unroll of the pair-symmetric kernel
 #endif
-#ifndef RMB_SYM_PER_UNROLL
-#define RMB_SYM_PER_UNROLL 2  // non-central image boxes of the pair-symmetric pseudo-periodic kernels (PER == 2)
-#endif
 #ifndef RMB_SYM_NT
 #define RMB_SYM_NT 1      // blobs per lane of the pair-symmetric kernel (1 or 2; TILE must be a multiple of 128 NT).
                           // Measured at N = 400k: 334.6 (1) vs 336.8 (2) G pairs/s, and 270 vs 252 at N = 20k
@@ -358,6 +355,9 @@ struct SymArgs {
   int n_tiles;
   int rows, chunk;                // row groups of this launch; tiles per work item (sym_item)
   int row_first, row_stride;      // row groups handled by this launch: row_first + k * row_stride, k < rows
+  int pad_[3];                    // keeps K at an offset = 8 mod 16 in the parameter bank: with K 16-byte aligned nvcc 12.9
+                                  // re-loads one more constant pair inside the pair loop (126 instead of 125 instructions;
+                                  // measured 335.6 vs 338.3 G pairs/s, profiles/r02c_item_decode_ab.jsonl)
   UfCtx<double> K;
   // PER instantiations only (pseudo-periodic in x and/or y; records then hold unscaled positions)
   Periodic<double> P;
@@ -415,7 +415,7 @@ __device__ __forceinline__ void sym_pair(double rx, double ry, double rz, double
   }
 }
 
-template <int PER>
+template <bool PER>
 __device__ __forceinline__ void sym_geometry(const SymArgs& A, double xi, double yi, double hi, const double* w,
                                              double& rx, double& ry, double& rz, double& hj)
 {
@@ -431,11 +431,11 @@ __device__ __forceinline__ void sym_geometry(const SymArgs& A, double xi, double
   rz = hi - hj;
 }
 
-// PER: 0 open boundaries; 1 pseudo-periodic, every image box tested for overlapping pairs; 2 pseudo-periodic with
-// L >= 4a in every periodic direction (host-checked): after the minimum-image wrap |r_d| <= L_d / 2, so a pair in a
-// non-central box is at least L_d / 2 >= 2a apart -- only the central box (first in SymArgs::box) can hold an
-// overlapping pair; the other boxes run the far-field code with no vote, no select and no branch.
-template <int BLOCK, int NT, int K0, int NK, bool TAIL, bool WALL, int PER>
+// (r02: an instantiation that runs the non-central image boxes through far-field-only code -- legal when L >= 4a,
+// since after the minimum-image wrap only the central box can hold an overlapping pair -- was measured at 348-360
+// against 356-358 G pairs/s for this loop, profiles/r02a_per_far_boxes_ab.jsonl: the per-box vote + branch is not
+// what bounds the kernel, and the variant was dropped.)
+template <int BLOCK, int NT, int K0, int NK, bool TAIL, bool WALL, bool PER>
 __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int lane,
                                           SymLane<NT, SymRec<BLOCK>::NV>& L, const SymArgs& A,
                                           double* __restrict__ acc_j, long i0, long j0)
@@ -464,7 +464,7 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
         const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
         const bool any_near = __any_sync(0xffffffffu, lt4(r2));
         sym_pair<BLOCK, WALL, true>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
-      } else if (PER == 1) {
+      } else {
         const T Rz = hi + hj, rz2 = rz * rz;
 #pragma unroll 1
         for (int b = 0; b < A.box.n; b++) {
@@ -472,20 +472,6 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
           const T r2 = RMB_FMA(by, by, RMB_FMA(bx, bx, rz2));
           const bool any_near = __any_sync(0xffffffffu, lt4(r2));
           sym_pair<BLOCK, WALL, true>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
-        }
-      } else {
-        const T Rz = hi + hj, rz2 = rz * rz;
-        {
-          const T r2 = RMB_FMA(ry, ry, RMB_FMA(rx, rx, rz2));
-          const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-          sym_pair<BLOCK, WALL, true>(rx, ry, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
-        }
-        constexpr int PU = RMB_SYM_PER_UNROLL;
-#pragma unroll PU
-        for (int b = 1; b < A.box.n; b++) {
-          const T bx = rx + A.box.s[b][0], by = ry + A.box.s[b][1];
-          const T r2 = RMB_FMA(by, by, RMB_FMA(bx, bx, rz2));
-          sym_pair<BLOCK, WALL, true>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, false, r2, L.u[k], aj);
         }
       }
     }
@@ -500,8 +486,7 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
 
 // Diagonal block (J == the block of blob k): ordered pairs (l, (l + s) & 31), s = 1..31, one direction.
 // PER: also s = 0, the blob's own images in the non-central boxes.
-// (the diagonal block is 1 / n_blocks of the work: the generic box loop serves PER == 1 and PER == 2)
-template <int BLOCK, int NT, bool TAIL, bool WALL, int PER>
+template <int BLOCK, int NT, bool TAIL, bool WALL, bool PER>
 __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lane, SymLane<NT, SymRec<BLOCK>::NV>& L, int k,
                                          const SymArgs& A, long i0)
 {
@@ -538,7 +523,7 @@ __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lan
   }
 }
 
-template <int BLOCK, bool TMA, int NT, bool WALL, int PER>
+template <int BLOCK, bool TMA, int NT, bool WALL, bool PER>
 __global__ void __launch_bounds__(TPB, RMB_SYM_MINB(BLOCK)) sym_kernel(const __grid_constant__ SymArgs A)
 {
   typedef double T;
@@ -552,11 +537,17 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB(BLOCK)) sym_kernel(const __g
   // (broadcasting `warp` with __shfl_sync makes the block index provably uniform and removes the BRA.DIV / WARPSYNC
   // guards around the shuffles -- 125 -> 122 instructions per step -- but measured 3.6 % SLOWER: 338 -> 326 G pairs/s)
   // this CTA's work item: row group g of ROW blobs x the tiles [v0, v1) of its row [g * ROW / TILE, n_tiles)
-  const SymItem item = sym_item((int)blockIdx.x, (int)blockIdx.y, A.rows, A.row_first, A.row_stride, ROW, TILE,
-                                A.n_tiles, A.chunk);
+  // Decoded by one thread and broadcast through shared memory: with the decode inlined in every thread nvcc 12.9
+  // allocates 96 instead of 92 registers and schedules the pair loop 3 % slower (328 vs 338 G pairs/s at N = 400k,
+  // profiles/r02c_item_decode_ab.jsonl) although the loop's instructions are the same.
+  __shared__ SymItem s_item;
+  if (tid == 0) s_item = sym_item((int)blockIdx.x, (int)blockIdx.y, A.rows, A.row_first, A.row_stride, ROW, TILE,
+                                  A.n_tiles, A.chunk);
+  __syncthreads();
+  const SymItem item = s_item;
   if (!item.valid) return;
-  const long g = item.g;
-  const long I0 = (g * (TPB / 32) + warp) * NT;            // this warp's first block of 32
+  const int g = (int)item.g;
+  const long I0 = ((long)g * (TPB / 32) + warp) * NT;      // this warp's first block of 32
 
   constexpr int NV = SymRec<BLOCK>::NV;
   const T* srcw = A.src;
@@ -813,19 +804,6 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
   }
   A.inva = 1.0 / c.a;
   A.box = make_box_table<double>(A.P, 1.0 / c.a);
-  // the central box first (PER == 2 treats it apart); far-only non-central boxes need L >= 4a
-  bool far_boxes = per;
-  for (int d = 0; d < 2; d++)
-    if (A.P.per[d] && c.L[d] < 4.0 * c.a) far_boxes = false;
-  if (per && A.box.central != 0) {
-    for (int d = 0; d < 3; d++) {
-      const double t = A.box.s[0][d];
-      A.box.s[0][d] = A.box.s[A.box.central][d];
-      A.box.s[A.box.central][d] = t;
-    }
-    A.box.central = 0;
-  }
-  const int pm = per ? ((far_boxes && !(c.flags & RMB_NO_FAR_BOXES)) ? 2 : 1) : 0;
   const long rows_all = n_pad / (TPB * RMB_SYM_NT);
   const long rows = (rows_all - row_first + row_stride - 1) / row_stride;
   if (rows > 0) {
@@ -838,16 +816,12 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
     const int gy = sym_grid_y(A.rows, row_first, row_stride, TPB * NT, TILE, p.n_tiles, A.chunk);
     if (gy > 65535) return fail(RMB_E_ARG, "pair-symmetric product: too many chunks per row pair");
     const dim3 grid((unsigned)((rows + 1) / 2), (unsigned)gy);
-#define RMB_SYM_LAUNCH_W(B, W)                                                              \
-    do {                                                                                   \
-      if (pm == 2) sym_kernel<B, true, NT, W, 2><<<grid, TPB, 0, c.stream>>>(A);            \
-      else if (pm == 1) sym_kernel<B, true, NT, W, 1><<<grid, TPB, 0, c.stream>>>(A);       \
-      else sym_kernel<B, true, NT, W, 0><<<grid, TPB, 0, c.stream>>>(A);                    \
-    } while (0)
 #define RMB_SYM_LAUNCH(B)                                                                  \
     do {                                                                                   \
-      if (wall) RMB_SYM_LAUNCH_W(B, true);                                                 \
-      else RMB_SYM_LAUNCH_W(B, false);                                                     \
+      if (wall && per) sym_kernel<B, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);   \
+      else if (wall) sym_kernel<B, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);    \
+      else if (per) sym_kernel<B, true, NT, false, true><<<grid, TPB, 0, c.stream>>>(A);     \
+      else sym_kernel<B, true, NT, false, false><<<grid, TPB, 0, c.stream>>>(A);             \
     } while (0)
     if (c.block == RMB_UF_UT) {
       RMB_SYM_LAUNCH(UF_UT);
@@ -856,13 +830,13 @@ int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
     } else if (c.block == RMB_UT || (c.block == RMB_WF && !wall)) {   // free space: WF is the same function as UT
       RMB_SYM_LAUNCH(UT);
     } else if (c.block == RMB_WF) {
-      RMB_SYM_LAUNCH_W(WF, true);
-    } else if (pm == 0 && wall && (c.flags & RMB_NO_TMA)) {
-      sym_kernel<UF, false, NT, true, 0><<<grid, TPB, 0, c.stream>>>(A);
-    } else {
-      RMB_SYM_LAUNCH(UF);
-    }
-#undef RMB_SYM_LAUNCH_W
+      if (per) sym_kernel<WF, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
+      else sym_kernel<WF, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
+    } else if (per && wall) sym_kernel<UF, true, NT, true, true><<<grid, TPB, 0, c.stream>>>(A);
+    else if (per) sym_kernel<UF, true, NT, false, true><<<grid, TPB, 0, c.stream>>>(A);
+    else if (!wall) sym_kernel<UF, true, NT, false, false><<<grid, TPB, 0, c.stream>>>(A);
+    else if (c.flags & RMB_NO_TMA) sym_kernel<UF, false, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
+    else sym_kernel<UF, true, NT, true, false><<<grid, TPB, 0, c.stream>>>(A);
 #undef RMB_SYM_LAUNCH
   }
   e = cudaGetLastError();

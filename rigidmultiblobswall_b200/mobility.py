@@ -29,7 +29,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import (DETERMINISTIC, FP32, FP64, FREE_SURFACE, IN_PLANE, NO_FAR_BOXES, NO_TMA, NO_WALL, SINGLE_WALL,  # noqa: F401
+from ._lib import (DETERMINISTIC, FP32, FP64, FREE_SURFACE, IN_PLANE, NO_TMA, NO_WALL, SINGLE_WALL,  # noqa: F401
                    SYMMETRIC, UF,
                    UF_UT, UT, WF, WT)
 

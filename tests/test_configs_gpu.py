@@ -71,7 +71,7 @@ def test_c3_rollers_100k_all_blocks_random_rows_against_the_oracle():
     refs = {}
     for name, blk, vec, vp in (("UF", mb.UF, fd, fp), ("UT", mb.UT, td, tp), ("WF", mb.WF, fd, fp), ("WT", mb.WT, td, tp)):
         refs[name] = oracle.mobility_product(name, "single_wall", rp, vp, eta, a, L, targets=(0, 256))
-        for flags in (0, mb.DETERMINISTIC, mb.NO_FAR_BOXES):   # default pair-symmetric, row kernel, generic box loop
+        for flags in (0, mb.DETERMINISTIC):                    # default (pair-symmetric) kernel, row kernel
             u = mb.mobility_product(blk, mb.SINGLE_WALL, rd, vec, eta, a, periodic_length=L, flags=flags)
             assert relerr(rows3(u, idx), refs[name]) < 1e-12, (name, flags)
     u = mb.single_wall_mobility_trans_times_force_torque_b200(rd, fd, td, eta, a, periodic_length=L)

@@ -3,7 +3,7 @@ command ncu is pointed at (`ncu ... python tools/run_case.py <case> --n N --reps
 
   python tools/run_case.py CASE[,CASE...] [--n N] [--reps R] [--warm W] [--cloud dilute|dense|c1box|c3]
 
-CASE = <block>_<wall>_<boundary>_<precision>[_row|_sym|_nofar]   block UF|UT|WF|WT|UFUT, wall wall|free|fs,
+CASE = <block>_<wall>_<boundary>_<precision>[_row|_sym]   block UF|UT|WF|WT|UFUT, wall wall|free|fs,
        boundary open|xy|x, precision f64|f32;  or st_<wall>_<boundary>_<precision> (source-target, radii +-40 %)
 RMB_LIB=<variant .so> selects a tuning build (tools/build_tune.py)."""
 import argparse, json, os, sys
@@ -46,7 +46,7 @@ for case in args.cases.split(","):
         L = Lc3
     boxes = {"open": 1, "xy": 9, "x": 3}[bnd]
     P = mb.FP64 if prec == "f64" else mb.FP32
-    fl = {"": 0, "row": mb.DETERMINISTIC, "sym": mb.SYMMETRIC, "nofar": mb.NO_FAR_BOXES}[mode]
+    fl = {"": 0, "row": mb.DETERMINISTIC, "sym": mb.SYMMETRIC}[mode]
     if st:
         fn = lambda: mb.mobility_source_target(W, rd, rd, fd, rad, rad, eta, periodic_length=L, precision=P)
     else:
