@@ -8,7 +8,7 @@ KEEP = re.compile(r"^(dram__bytes_(read|write)\.sum$|gpu__time_duration\.sum|lau
                   r"\.avg\.pct_of_peak_sustained_active|sm__pipe_fp64_cycles_active\.avg\.pct|sm__throughput\.avg\.pct|"
                   r"sm__warps_active\.avg\.pct_of_peak_sustained_active|smsp__average_warps_issue_stalled_.*_per_issue_active|"
                   r"smsp__inst_executed\.sum$|smsp__inst_executed_pipe_fp64\.sum$|sm__inst_executed_pipe_fp64\.sum$|smsp__issue_active\.avg\.pct|"
-                  r"l1tex__data_pipe_lsu_wavefronts_mem_shared\.sum$|sm__cycles_elapsed\.max|lts__t_sector_hit_rate\.pct|smsp__cycles_active\.avg$|sm__inst_executed\.sum$)")
+                  r"l1tex__data_pipe_lsu_wavefronts_mem_shared\.sum$|sm__pipe_(fma|fmaheavy|alu)_cycles_active\.avg\.pct_of_peak_sustained_active|sm__inst_executed_pipe_fmaheavy\.avg\.pct_of_peak_sustained_active|sm__cycles_elapsed\.max|lts__t_sector_hit_rate\.pct|smsp__cycles_active\.avg$|sm__inst_executed\.sum$)")
 
 def full(path):
     out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
@@ -19,6 +19,21 @@ def full(path):
             print("# kernel:", v)
         if KEEP.search(n):
             print("%-90s %-16s %s" % (n, u, v))
+
+def raw(path):
+    """same summary from the CSV of `ncu -i x.ncu-rep --page raw --csv` (what tools/gpu_session.sh brings back: the
+    .ncu-rep files themselves are ~15 MB each and gpurun_out is capped at 64 MiB)"""
+    rows = list(csv.reader(open(path)))
+    names, units = rows[0], rows[1]
+    for vals in rows[2:]:
+        for n, u, v in zip(names, units, vals):
+            if n == "Kernel Name":
+                print("# kernel:", v)
+            if KEEP.search(n) and not re.search(r"\.(max|min|sum)\.pct|per_second|_allocated", n):
+                if "stalled" in n and float(v.replace(",", "")) < 0.3:
+                    continue
+                print("%-90s %-16s %s" % (n, u, v))
+
 
 def launches(path):
     txt = open(path).read()
@@ -61,4 +76,4 @@ def kernels(path, pairs=None):
 if sys.argv[1] == "kernels":
     kernels(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else None)
 else:
-    {"full": full, "list": launches}[sys.argv[1]](sys.argv[2])
+    {"full": full, "list": launches, "raw": raw}[sys.argv[1]](sys.argv[2])
