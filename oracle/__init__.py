@@ -57,6 +57,7 @@ def lib():
         _lib.rmb_oracle_uf_wall_fast.argtypes = [ctypes.c_long, dp, dp, ctypes.c_double, ctypes.c_double,
                                                  ctypes.c_long, ctypes.c_long, dp]
         _lib.rmb_oracle_threads.restype = ctypes.c_int
+        _lib.rmb_oracle_set_threads.argtypes = [ctypes.c_int]
         _lib.rmb_oracle_source_target.argtypes = [ctypes.c_int, ctypes.c_long, ctypes.c_long, dp, dp, dp, dp, dp,
                                                   ctypes.c_double, dp, dp]
         _lib.rmb_oracle_source_target_wall_wrap.argtypes = [ctypes.c_long, ctypes.c_long, dp, dp, dp, dp, dp,
@@ -70,6 +71,20 @@ def _p(x):
 
 def threads():
     return int(lib().rmb_oracle_threads())
+
+
+def host_cores():
+    """CPUs this process may run on (torchrun does not restrict the affinity, it only exports OMP_NUM_THREADS=1)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def set_threads(n=None):
+    """Use n (default: all host cores) OpenMP threads whatever OMP_NUM_THREADS says."""
+    lib().rmb_oracle_set_threads(int(n or host_cores()))
+    return threads()
 
 
 def mobility_product(block, wall, r_vectors, vec, eta, a, periodic_length=None,

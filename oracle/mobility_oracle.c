@@ -368,6 +368,16 @@ int rmb_oracle_threads(void)
 #endif
 }
 
+/* torchrun exports OMP_NUM_THREADS=1 to its workers: the CPU legs of bench.py set the thread count themselves */
+void rmb_oracle_set_threads(int n)
+{
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 /*
  * Timing variant of the flagship block only (single-wall UF, no periodic
  * images; mobility_numba.py:124-287): the same expressions as free_uf() +

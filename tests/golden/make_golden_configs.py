@@ -29,31 +29,8 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, ROOT)
 
 from oracle import make_ref  # noqa: E402
+from oracle.ref_driver import build_bodies, gmres_right  # noqa: E402
 import bench  # noqa: E402
-
-
-def build_bodies(mbod, ref_cfg, loc, quat, a):
-    from body import body
-    from quaternion_integrator.quaternion import Quaternion
-    bodies = []
-    for k in range(len(loc)):
-        b = body.Body(loc[k], Quaternion(quat[k]), ref_cfg, a)
-        b.mobility_blobs = mbod.set_mobility_blobs("python")
-        b.ID = "body"
-        bodies.append(b)
-    return bodies
-
-
-def gmres_right(lin, PC, RHS, tol):
-    """general_application_utils.gmres:600-635 restated for the installed SciPy (rtol=): A' = A P^-1, x = P^-1 y."""
-    n = RHS.size
-    nrm = np.linalg.norm(RHS)
-    its = [0]
-    A_LO = spla.LinearOperator((n, n), matvec=lambda y: lin(PC(y)), dtype="float64")
-    y, info = spla.gmres(A_LO, RHS / nrm, rtol=tol, atol=0, restart=60, maxiter=1000,
-                         callback=lambda r: its.__setitem__(0, its[0] + 1), callback_type="pr_norm")
-    sol = PC(y) * nrm
-    return sol, info, its[0], np.linalg.norm(lin(sol) - RHS) / nrm
 
 
 def main():
