@@ -9,7 +9,9 @@ The reference selects its Mf implementation by string:
                                                                   multi_bodies.py:99-102
 register() makes all three reach the B200 kernels without editing the reference:
   * every `<name>_b200` / `<name>_b200_fp32` function is attached to the reference's `mobility` module;
-  * set_mobility_vector_prod is wrapped to accept 'b200', 'b200_no_wall', 'b200_fp32', 'b200_no_wall_fp32';
+  * set_mobility_vector_prod is wrapped to accept 'b200', 'b200_no_wall', 'b200_free_surface' (+ '_fp32' of each)
+    and the per-blob-radii family 'radii_b200', 'radii_b200_no_wall', 'radii_b200_free_surface' (which, like the
+    reference's 'radii_numba*' strings, multi_bodies.py:262-287, bind the radii of kwargs['bodies']);
   * set_mobility_blobs (the DENSE blob mobility of one body, multi_bodies.py:205-227, input-file key
     `mobility_blobs_implementation`, read_input.py:65) is wrapped to accept 'b200' and 'b200_no_wall';
   * optionally (alias_pycuda=True) the `<name>_pycuda` attributes of the mobility module are pointed at the B200
@@ -18,13 +20,27 @@ register() makes all three reach the B200 kernels without editing the reference:
 """
 import functools
 
+import numpy as np
+
 from . import mobility as _mb
 
+# string -> function name: the B200 twins of the reference's 'numba' / 'numba_no_wall' / 'numba_free_surface'
+# (multi_bodies.py:246-261)
 IMPLEMENTATIONS = {
     "b200": "single_wall_mobility_trans_times_force_b200",
     "b200_fp32": "single_wall_mobility_trans_times_force_b200_fp32",
     "b200_no_wall": "no_wall_mobility_trans_times_force_b200",
     "b200_no_wall_fp32": "no_wall_mobility_trans_times_force_b200_fp32",
+    "b200_free_surface": "free_surface_mobility_trans_times_force_b200",
+    "b200_free_surface_fp32": "free_surface_mobility_trans_times_force_b200_fp32",
+}
+
+# the twins of 'radii_numba' / 'radii_numba_no_wall' / 'radii_numba_free_surface' (multi_bodies.py:262-287): a
+# source-target product bound to the bodies' own blob radii through mobility_radii_trans_times_force
+RADII_IMPLEMENTATIONS = {
+    "radii_b200": "single_wall_mobility_trans_times_force_source_target_b200",
+    "radii_b200_no_wall": "no_wall_mobility_trans_times_force_source_target_b200",
+    "radii_b200_free_surface": "free_surface_mobility_trans_times_force_source_target_b200",
 }
 
 
@@ -65,6 +81,12 @@ def register(multi_bodies_module, alias_pycuda=False):
     def set_mobility_vector_prod(implementation, *args, **kwargs):
         if implementation in IMPLEMENTATIONS:
             return getattr(_mb, IMPLEMENTATIONS[implementation])
+        if implementation in RADII_IMPLEMENTATIONS:
+            # multi_bodies.py:279-286: the radii of every blob of kwargs['bodies'], in blob order
+            radius_blobs = np.concatenate([np.asarray(b.blobs_radius, dtype=np.float64).reshape(-1)
+                                           for b in kwargs.get("bodies")], axis=0)
+            return functools.partial(_mb.mobility_radii_trans_times_force, radius_blobs=radius_blobs,
+                                     function=getattr(_mb, RADII_IMPLEMENTATIONS[implementation]))
         return original(implementation, *args, **kwargs)
 
     set_mobility_vector_prod._b200_wrapped = True

@@ -31,6 +31,18 @@ def test_implementation_strings_resolve_in_the_reference_driver(multi_bodies):
     assert multi_bodies.set_mobility_vector_prod("b200") is mb.single_wall_mobility_trans_times_force_b200
     assert multi_bodies.set_mobility_vector_prod("b200_no_wall") is mb.no_wall_mobility_trans_times_force_b200
     assert multi_bodies.set_mobility_vector_prod("b200_fp32") is mb.single_wall_mobility_trans_times_force_b200_fp32
+    assert multi_bodies.set_mobility_vector_prod("b200_free_surface") is mb.free_surface_mobility_trans_times_force_b200
+    # the per-blob-radii family binds the radii of kwargs['bodies'] like the reference's 'radii_numba*' (:262-287)
+    import numpy as np
+
+    class B:
+        blobs_radius = np.array([0.1, 0.2])
+    for name, fn in (("radii_b200", mb.single_wall_mobility_trans_times_force_source_target_b200),
+                     ("radii_b200_no_wall", mb.no_wall_mobility_trans_times_force_source_target_b200),
+                     ("radii_b200_free_surface", mb.free_surface_mobility_trans_times_force_source_target_b200)):
+        p = multi_bodies.set_mobility_vector_prod(name, bodies=[B(), B()])
+        assert p.func is mb.mobility_radii_trans_times_force and p.keywords["function"] is fn
+        assert p.keywords["radius_blobs"].tolist() == [0.1, 0.2, 0.1, 0.2]
     # dense blob mobility of one body (mobility_blobs_implementation, multi_bodies.py:205-227)
     assert multi_bodies.set_mobility_blobs("python") is multi_bodies.mb.single_wall_fluid_mobility
     assert multi_bodies.set_mobility_blobs("b200") is mb.single_wall_fluid_mobility_b200

@@ -27,7 +27,7 @@ rates) echo "== rates"
   timeout 600 python tools/run_case.py UF_wall_open_f64,UF_wall_open_f64_row,UF_wall_open_f32,WT_wall_open_f64,st_wall_open_f64 --n 200000 --cloud dense 2>&1 | tail -1 | tee gpurun_out/${T}_rates_dense.json
   timeout 600 python tools/run_case.py UF_wall_open_f64,UF_wall_open_f64_row,UF_wall_open_f32,WT_wall_open_f64,st_wall_open_f64 --n 200000 --cloud c1box 2>&1 | tail -1 | tee gpurun_out/${T}_rates_c1box.json;;
 ncu) echo "== ncu full captures"
-  for spec in "UF_wall_open_f64:200000:sym_kernel:flagship" "UF_wall_xy_f64:100000:sym_kernel:uf_xy" "st_wall_open_f64:100000:st_kernel:st_wall" "UF_wall_open_f32:200000:mf_kernel:uf_f32" "UF_wall_open_f64_row:200000:mf_kernel:uf_row"; do
+  for spec in ${NCU_SPECS:-"UF_wall_open_f64:200000:sym_kernel:flagship" "UF_wall_xy_f64:100000:sym_kernel:uf_xy"}; do
     IFS=: read c n k name <<< "$spec"
     timeout 600 $NCU_FULL -k regex:$k -s 1 -c 1 -o /tmp/${T}_${name}_full -f python tools/run_case.py $c --n $n --reps 1 --warm 1 > gpurun_out/${T}_${name}_ncu.log 2>&1; echo "$name rc=$?"
     # the .ncu-rep files are ~15 MB each and gpurun_out is capped at 64 MiB: keep the raw page as CSV (and the source page of the flagship)
@@ -35,25 +35,8 @@ ncu) echo "== ncu full captures"
     [ $name = flagship ] && ncu -i /tmp/${T}_${name}_full.ncu-rep --page source --csv > gpurun_out/${T}_${name}_source.csv 2>/dev/null
   done
   echo "== launch list"; ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches.csv python bench.py --n 200000 --steps 2 --warmup 1 --no-cpu > gpurun_out/${T}_ncu_launch.log 2>&1; echo "rc=$?";;
-ab2) echo "== A/B of decode variants"
-  for so in build_tune/r01.so build_tune/c0_nopad.so build_tune/c1_pad3.so build_tune/c2_smem.so build_tune/c4_nopair.so build_tune/c2_smem_nopad.so build_tune/c4_nopair_nopad.so build_tune/r01_w200.so; do
-    export RMB_LIB=$PWD/$so
-    timeout 300 python tools/run_case.py UF_wall_open_f64,WT_wall_open_f64,UF_wall_xy_f64 --n 400000 --reps 3 2>&1 | tail -1
-    timeout 300 python tools/time_rank_share.py 8 1000000 2>&1 | tail -1
-  done | tee gpurun_out/${T}_ab2.jsonl; unset RMB_LIB;;
-ab) echo "== A/B r01 library vs this build (same box)"
-  nvidia-smi --query-gpu=clocks.sm,clocks.max.sm,power.draw,power.limit,clocks_event_reasons.active --format=csv
-  for so in build_tune/r01.so default build_tune/r01.so default; do
-    [ $so = default ] && unset RMB_LIB || export RMB_LIB=$PWD/$so
-    timeout 300 python tools/run_case.py UF_wall_open_f64,UF_wall_open_f64_row,WT_wall_open_f64 --n 400000 --reps 4 2>&1 | tail -1
-    timeout 300 python tools/run_case.py UF_wall_open_f64 --n 1000000 --reps 2 --warm 1 2>&1 | tail -1
-  done | tee gpurun_out/${T}_ab.jsonl; unset RMB_LIB
-  echo "== light ncu metrics, both libraries"
-  for so in build_tune/r01.so default; do
-    [ $so = default ] && unset RMB_LIB || export RMB_LIB=$PWD/$so
-    ncu --metrics sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active,smsp__inst_executed.sum,gpu__time_duration.sum,launch__registers_per_thread,launch__grid_size,sm__warps_active.avg.pct_of_peak_sustained_active,lts__t_sector_hit_rate.pct,dram__bytes_read.sum,l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum --clock-control none -k regex:sym_kernel -s 1 -c 1 --csv --log-file gpurun_out/${T}_ab_ncu_$(basename $so .so).csv python tools/run_case.py UF_wall_open_f64 --n 400000 --reps 1 --warm 1 > /dev/null 2>&1; echo "rc=$?"
-  done; unset RMB_LIB
-  (nvidia-smi --query-gpu=clocks.sm,power.draw,clocks_event_reasons.active --format=csv -lms 500 > gpurun_out/${T}_smi.csv &) ; python tools/run_case.py UF_wall_open_f64 --n 1000000 --reps 3 --warm 1 | tail -1; pkill -n nvidia-smi; tail -8 gpurun_out/${T}_smi.csv;;
+traffic) echo "== DRAM traffic of one flagship launch at N = 1M"
+  timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:sym_kernel -s 1 -c 1 --csv --log-file gpurun_out/${T}_traffic_n1m.csv python tools/run_case.py UF_wall_open_f64 --n 1000000 --reps 1 --warm 1 > gpurun_out/${T}_traffic.log 2>&1; echo "rc=$?"; tail -4 gpurun_out/${T}_traffic_n1m.csv;;
 esac
 done
 ls -la gpurun_out | tail -30
