@@ -33,7 +33,10 @@ def test_reference_mobility_problem_with_the_b200_product_selected_by_string(mbo
     from oracle import ref_driver
     from rigidmultiblobswall_b200 import mobility as mb
     ref_cfg, loc, quat, FT, a, eta, tol = bench.make_c2(n_bodies)
-    loc[3, 2] = 1.2                                           # one body close to the wall: blobs with z < a
+    # one body so close to the wall that its lowest blob sits at z = 0.4 a: the clamp + damping path runs
+    from rigidmultiblobswall_b200 import rigid
+    z3 = rigid.RigidBodies(ref_cfg, loc, quat).get_r_vectors().reshape(-1, 3)[45:60, 2].min().item()
+    loc[3, 2] -= z3 - 0.4 * a
     assert mbod.set_mobility_vector_prod("b200") is mb.single_wall_mobility_trans_times_force_b200
     out = {}
     for impl in ("python", "numba", "b200"):
