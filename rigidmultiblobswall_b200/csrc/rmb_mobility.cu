@@ -77,6 +77,9 @@ namespace {
 #ifndef RMB_WAVES
 #define RMB_WAVES 10
 #endif
+#ifndef RMB_MIN_SPLIT_SRC
+#define RMB_MIN_SPLIT_SRC 64   // fewest sources one blockIdx.y of the row kernel handles (a multiple of 32; r01: 1024)
+#endif
 constexpr int TPB = RMB_TPB;    // targets (threads) per CTA
 constexpr int TILE = RMB_TILE;  // sources per shared-memory tile
 constexpr int STAGES = 2;
@@ -144,9 +147,8 @@ struct MfArgs {
   long n_src, n_tgt, tgt_off;
   Periodic<T> P;
   T inva;
-  int n_tiles;       // ceil(n_src / TILE)
-  int n_vt;          // = n_tiles (image boxes are looped inside the pair loop)
-  int vt_per_split;  // tiles handled by one blockIdx.y
+  int n_tiles;       // ceil(n_src / TILE); the records are zero-padded to n_tiles * TILE
+  int src_per_split; // sources handled by one blockIdx.y (a multiple of 32; streamed in tiles of <= TILE records)
   int n_split;
   T* partial;        // [n_split][n_tgt][3] when n_split > 1
   double* out;       // [n_tgt][3], written here when n_split == 1
@@ -221,7 +223,6 @@ __global__ void __launch_bounds__(TPB, RMB_MINB) mf_kernel(const __grid_constant
 {
   constexpr int NV = (BLOCK == UF_UT) ? 2 : 1;
   constexpr int W = RecWords<T, NV>::value;
-  constexpr uint32_t TILE_BYTES = TILE * W * sizeof(T);
   __shared__ alignas(128) T tile[TMA ? STAGES : 1][TILE * W];
   __shared__ alignas(8) uint64_t full[STAGES];
 
@@ -239,9 +240,12 @@ __global__ void __launch_bounds__(TPB, RMB_MINB) mf_kernel(const __grid_constant
   }
   UfCtx<T> C = A.K;
   set_target_height(C, t.h);
-  const int v0 = blockIdx.y * A.vt_per_split;
-  const int v1 = min(v0 + A.vt_per_split, A.n_vt);
-  const T* srcw = reinterpret_cast<const T*>(A.src);
+  // this CTA's sources [s0, s1): tiles of TILE records, the last one possibly shorter (records are padded to n_tiles * TILE)
+  const long s0 = (long)blockIdx.y * A.src_per_split;
+  const long s1 = min(s0 + (long)A.src_per_split, (long)A.n_tiles * TILE);
+  const int v0 = 0, v1 = (int)((s1 - s0 + TILE - 1) / TILE);
+  const T* srcw = reinterpret_cast<const T*>(A.src) + (size_t)s0 * W;
+  auto tile_records = [&](int v) { return (uint32_t)min((long)TILE, s1 - s0 - (long)v * TILE); };
 
   if (TMA) {
     if (tid == 0) {
@@ -251,8 +255,9 @@ __global__ void __launch_bounds__(TPB, RMB_MINB) mf_kernel(const __grid_constant
     }
     __syncthreads();
     if (tid == 0 && v0 < v1) {
-      mbar_expect_tx(&full[0], TILE_BYTES);
-      bulk_g2s(tile[0], srcw + (size_t)v0 * TILE * W, TILE_BYTES, &full[0]);
+      const uint32_t bytes = tile_records(v0) * W * sizeof(T);
+      mbar_expect_tx(&full[0], bytes);
+      bulk_g2s(tile[0], srcw + (size_t)v0 * TILE * W, bytes, &full[0]);
     }
   }
 
@@ -264,18 +269,20 @@ __global__ void __launch_bounds__(TPB, RMB_MINB) mf_kernel(const __grid_constant
     if (TMA) {
       // stage^1 was last read in iteration v-1, which ended with __syncthreads
       if (tid == 0 && v + 1 < v1) {
-        mbar_expect_tx(&full[stage ^ 1], TILE_BYTES);
-        bulk_g2s(tile[stage ^ 1], srcw + (size_t)(v + 1) * TILE * W, TILE_BYTES, &full[stage ^ 1]);
+        const uint32_t bytes = tile_records(v + 1) * W * sizeof(T);
+        mbar_expect_tx(&full[stage ^ 1], bytes);
+        bulk_g2s(tile[stage ^ 1], srcw + (size_t)(v + 1) * TILE * W, bytes, &full[stage ^ 1]);
       }
       mbar_wait(&full[stage], (phases >> stage) & 1u);
       phases ^= (1u << stage);
     } else {
       const T* gsrc = srcw + (size_t)tl * TILE * W;
-      for (int k = tid; k < TILE * W; k += TPB) tile[0][k] = gsrc[k];
+      const int words = (int)tile_records(v) * W;
+      for (int k = tid; k < words; k += TPB) tile[0][k] = gsrc[k];
       __syncthreads();
     }
-    const long j0 = (long)tl * TILE;
-    const int cnt = (int)min((long)TILE, A.n_src - j0);
+    const long j0 = s0 + (long)tl * TILE;
+    const int cnt = (int)max(0L, min((long)tile_records(v), A.n_src - j0));
     const bool diag = (j0 < blk_g1) && (j0 + cnt > blk_g0);
     const T* tp = tile[TMA ? stage : 0];
     if (diag) tile_pairs<T, BLOCK, WALL, PERIODIC, true>(tp, cnt, j0, gi, t, C, A.P, A.box, A.inva, ux, uy, uz);
@@ -667,7 +674,7 @@ int sm_count()
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 struct Plan {
-  int n_tiles, n_boxes, n_vt, n_split, vt_per_split, tgt_blocks;
+  int n_tiles, n_boxes, n_split, src_per_split, tgt_blocks;
   size_t rec_bytes, off_damp, off_partial, off_acc, total;
 };
 
@@ -684,18 +691,21 @@ int make_plan(int block, int precision, long n_tgt, long n_src, const double* L,
   p.n_tiles = (int)((n_src + TILE - 1) / TILE);
   p.n_boxes = 1;
   if (L) for (int d = 0; d < 3; d++) if (L[d] > 0) p.n_boxes *= 3;
-  p.n_vt = p.n_tiles;   // image boxes are looped inside the pair loop, not as extra tiles
-  p.tgt_blocks = (int)((n_tgt + TPB - 1) / TPB);
-  // Source splitting (blockIdx.y): used when the target CTAs alone would give
-  // fewer than RMB_WAVES waves of resident CTAs (tail effect / idle SMs).  A
-  // split keeps >= 4 tiles so the prologue stays amortised.
+  p.tgt_blocks = (int)((n_tgt + TPB - 1) / TPB);   // (image boxes are looped inside the pair loop, not as extra tiles)
+  // Source splitting (blockIdx.y): used when the target CTAs alone would give fewer than RMB_WAVES waves of
+  // resident CTAs (tail effect / idle SMs).  A split is a multiple of 32 sources and keeps >= RMB_MIN_SPLIT_SRC of
+  // them: at N = 1,000 (8 target CTAs) that is 16 splits = 128 CTAs of 64 sources instead of 8 CTAs that each walk
+  // all 1,000 sources at one warp per scheduler.
+  const long n_pad = (long)p.n_tiles * TILE;
   const int resident = sms * (768 / TPB);
-  int split = (RMB_WAVES * resident + p.tgt_blocks - 1) / (p.tgt_blocks > 0 ? p.tgt_blocks : 1);
-  if (split > p.n_vt / 4) split = p.n_vt / 4;
+  long split = (RMB_WAVES * (long)resident + p.tgt_blocks - 1) / (p.tgt_blocks > 0 ? p.tgt_blocks : 1);
+  if (split > n_pad / RMB_MIN_SPLIT_SRC) split = n_pad / RMB_MIN_SPLIT_SRC;
   if (split < 1) split = 1;
-  p.vt_per_split = (p.n_vt + split - 1) / split;
-  if (p.vt_per_split < 1) p.vt_per_split = 1;   // empty source set
-  p.n_split = (p.n_vt + p.vt_per_split - 1) / p.vt_per_split;
+  long per = (n_pad + split - 1) / split;
+  per = (per + 31) / 32 * 32;
+  if (per < 32) per = 32;                         // empty source set
+  p.src_per_split = (int)per;
+  p.n_split = n_pad > 0 ? (int)((n_pad + per - 1) / per) : 1;
   p.rec_bytes = (size_t)p.n_tiles * TILE * W * word;
   p.off_damp = align_up(p.rec_bytes, 256);
   p.off_partial = align_up(p.off_damp + (size_t)n_src * sizeof(double), 256);
@@ -754,7 +764,7 @@ int launch(const Call& c)
   }
   A.inva = T(1.0 / c.a);
   A.box = make_box_table<T>(A.P, 1.0 / c.a);
-  A.n_tiles = p.n_tiles; A.n_vt = p.n_vt; A.vt_per_split = p.vt_per_split; A.n_split = p.n_split;
+  A.n_tiles = p.n_tiles; A.src_per_split = p.src_per_split; A.n_split = p.n_split;
   A.partial = reinterpret_cast<T*>(c.ws + p.off_partial);
   A.out = c.out;
   A.damp = damp;

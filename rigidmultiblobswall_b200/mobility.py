@@ -54,6 +54,50 @@ def _workspace(nbytes, dev):
     return ws
 
 
+class _HostStage:
+    """Pinned staging of one NumPy-boundary call (what SciPy's GMRES makes at every iteration through the drop-in
+    functions): the inputs are packed into ONE pinned buffer and go up in one asynchronous copy, the result comes
+    down into a pinned buffer, and the stream is synchronised once.  One object per (device, stream, 3N); the
+    reference's PyCUDA path allocates and copies three arrays per call (mobility_pycuda.py:2249-2266)."""
+
+    def __init__(self, n3, dev):
+        self.h_in = torch.empty(3, n3, dtype=torch.float64).pin_memory()
+        self.h_in_np = self.h_in.numpy()
+        self.d_in = torch.empty(3, n3, dtype=torch.float64, device=dev)
+        self.h_out = torch.empty(n3, dtype=torch.float64).pin_memory()
+        self.h_out_np = self.h_out.numpy()
+        self.d_out = torch.empty(n3, dtype=torch.float64, device=dev)
+
+    def upload(self, arrays):
+        """arrays: up to three array-likes of 3N entries (any shape / stride / dtype); returns their device views"""
+        k = len(arrays)
+        for i, x in enumerate(arrays):
+            x = np.asarray(x)
+            if x.size != self.h_in_np.shape[1]:
+                raise ValueError("vector has %d entries, expected %d" % (x.size, self.h_in_np.shape[1]))
+            np.copyto(self.h_in_np[i], x.reshape(-1), casting="unsafe")
+        self.d_in[:k].copy_(self.h_in[:k], non_blocking=True)
+        return [self.d_in[i] for i in range(k)]
+
+    def download(self, count, dev):
+        self.h_out[:count].copy_(self.d_out[:count], non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        return self.h_out_np[:count].copy()
+
+
+_stages = {}
+
+
+def _stage(n3, dev):
+    key = (dev, torch.cuda.current_stream(dev).cuda_stream, n3)
+    st = _stages.get(key)
+    if st is None:
+        if len(_stages) > 8:                 # a handful of system sizes per process is the use case
+            _stages.clear()
+        st = _stages[key] = _HostStage(n3, dev)
+    return st
+
+
 def _as_device_f64(x, n3, dev):
     """(N,3)/flat/strided NumPy or torch -> contiguous flat float64 CUDA tensor (a copy only if needed)."""
     if isinstance(x, torch.Tensor):
@@ -78,12 +122,17 @@ def mobility_product(block, wall, r_vectors, vec, eta, a, periodic_length=None, 
     n = (r_vectors.numel() if isinstance(r_vectors, torch.Tensor) else np.asarray(r_vectors).size) // 3
     off, cnt = (0, n) if targets is None else targets
     with torch.cuda.device(dev):
-        r = _as_device_f64(r_vectors, 3 * n, dev)
-        va = _as_device_f64(vec, 3 * n, dev)
-        vb = _as_device_f64(vec_b, 3 * n, dev) if block == UF_UT else None
-        L = np.zeros(3) if periodic_length is None else np.asarray(
-            periodic_length.cpu() if isinstance(periodic_length, torch.Tensor) else periodic_length, dtype=np.float64)
-        Lc = (ctypes.c_double * 3)(*[float(x) for x in L.reshape(-1)[:3]])
+        stage = None
+        if host_in and out is None and n > 0 and not isinstance(vec, torch.Tensor):
+            stage = _stage(3 * n, dev)
+            ups = stage.upload([r_vectors, vec] + ([vec_b] if block == UF_UT else []))
+            r, va, vb = ups[0], ups[1], (ups[2] if block == UF_UT else None)
+            out = stage.d_out[:3 * cnt]
+        else:
+            r = _as_device_f64(r_vectors, 3 * n, dev)
+            va = _as_device_f64(vec, 3 * n, dev)
+            vb = _as_device_f64(vec_b, 3 * n, dev) if block == UF_UT else None
+        Lc = _length3(periodic_length)
         if out is None:
             out = torch.empty(3 * cnt, dtype=torch.float64, device=dev)
         if n > 0 and cnt > 0:
@@ -94,6 +143,8 @@ def mobility_product(block, wall, r_vectors, vec, eta, a, periodic_length=None, 
                 block, wall, precision, flags | default_flags, cnt, n, off,
                 r.data_ptr(), va.data_ptr(), vb.data_ptr() if vb is not None else None,
                 float(eta), float(a), Lc, out.data_ptr(), ws.data_ptr(), ws.numel(), stream))
+        if stage is not None:
+            return stage.download(3 * cnt, dev)
         return out.cpu().numpy() if host_in else out
 
 
@@ -177,9 +228,14 @@ def rotne_prager_tensor_b200(r_vectors, eta, a, *args, **kwargs):
     return dense_mobility(NO_WALL, r_vectors, eta, a)
 
 
+_ZERO_L = (ctypes.c_double * 3)(0.0, 0.0, 0.0)
+
+
 def _length3(periodic_length):
-    L = np.zeros(3) if periodic_length is None else np.asarray(
-        periodic_length.cpu() if isinstance(periodic_length, torch.Tensor) else periodic_length, dtype=np.float64)
+    if periodic_length is None:
+        return _ZERO_L
+    L = np.asarray(periodic_length.cpu() if isinstance(periodic_length, torch.Tensor) else periodic_length,
+                   dtype=np.float64)
     return (ctypes.c_double * 3)(*[float(x) for x in L.reshape(-1)[:3]])
 
 

@@ -35,6 +35,11 @@ ncu) echo "== ncu full captures"
     [ $name = flagship ] && ncu -i /tmp/${T}_${name}_full.ncu-rep --page source --csv > gpurun_out/${T}_${name}_source.csv 2>/dev/null
   done
   echo "== launch list"; ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches.csv python bench.py --n 200000 --steps 2 --warmup 1 --no-cpu --no-extra --profiling > gpurun_out/${T}_ncu_launch.log 2>&1; echo "rc=$?";;
+smalln) echo "== small-N latency: this build vs the r01 source split (>= 1024 sources per CTA)"
+  for so in default build_tune/split1024.so; do
+    [ $so = default ] && unset RMB_LIB || export RMB_LIB=$PWD/$so
+    timeout 300 python tools/time_small_n.py 1000 2000 5000 15000 50000 2>&1 | tail -1
+  done | tee gpurun_out/${T}_small_n.jsonl; unset RMB_LIB;;
 traffic) echo "== DRAM traffic of one flagship launch at N = 1M"
   timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:sym_kernel -s 1 -c 1 --csv --log-file gpurun_out/${T}_traffic_n1m.csv python tools/run_case.py UF_wall_open_f64 --n 1000000 --reps 1 --warm 1 > gpurun_out/${T}_traffic.log 2>&1; echo "rc=$?"; tail -4 gpurun_out/${T}_traffic_n1m.csv;;
 esac
