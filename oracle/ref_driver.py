@@ -32,7 +32,8 @@ def build_bodies(mbod, ref_cfg, loc, quat, a, blobs_implementation="python"):
     from quaternion_integrator.quaternion import Quaternion
     bodies = []
     for k in range(len(loc)):
-        b = body.Body(loc[k], Quaternion(quat[k]), ref_cfg, a)
+        cfg = ref_cfg[k] if isinstance(ref_cfg, (list, tuple)) else ref_cfg      # one geometry per body, or one for all
+        b = body.Body(loc[k], Quaternion(quat[k]), cfg, a)
         b.mobility_blobs = mbod.set_mobility_blobs(blobs_implementation)
         b.ID = "body"
         bodies.append(b)

@@ -21,6 +21,14 @@ def _nvcc():
     raise RuntimeError("nvcc not found: librmb_mobility.so cannot be built")
 
 
+def have_nvcc():
+    try:
+        _nvcc()
+        return True
+    except RuntimeError:
+        return False
+
+
 def stale():
     if not os.path.exists(SO):
         return True

@@ -23,9 +23,13 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
-    so = os.environ.get("RMB_LIB") or _build.SO      # RMB_LIB: tuning builds (tools/tune.sh)
-    if not os.path.exists(so):
-        _build.build()
+    so = os.environ.get("RMB_LIB")                   # RMB_LIB: tuning builds (tools/build_tune.py)
+    if not so:
+        so = _build.SO
+        # rebuild when a source is newer than the library (no-op when fresh); a machine without nvcc (the .so is
+        # shipped prebuilt to the GPU box) uses what is there, and a missing library with no compiler raises
+        if _build.stale() and (_build.have_nvcc() or not os.path.exists(so)):
+            _build.build()
     lib = ctypes.CDLL(so)
     c_dp = ctypes.c_void_p
     lib.rmb_version.restype = ctypes.c_int

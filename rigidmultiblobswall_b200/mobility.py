@@ -283,19 +283,30 @@ def symmetric_finish(r_vectors, vec, acc, eta, a, targets=None, out=None, flags=
     return out
 
 
+_DETERMINISTIC_DOC = ("\n    Extra keyword (not in the reference): deterministic=True forces the one-thread-per-target row kernel "
+                      "(fixed summation order, bit-reproducible, like the reference's per-row sum).  By default products "
+                      "of >= %d blobs use the pair-symmetric kernel, whose atomics make the last bits run-dependent."
+                      % 16384)
+
+
+def _kw_flags(kwargs, flags):
+    return flags | (DETERMINISTIC if kwargs.get("deterministic") else 0)
+
+
 def _make(block, wall, flags=0, precision=FP64, doc=""):
     def f(r_vectors, vec, eta, a, *args, **kwargs):
-        return mobility_product(block, wall, r_vectors, vec, eta, a,
-                                periodic_length=kwargs.get("periodic_length"), precision=precision, flags=flags)
-    f.__doc__ = doc
+        return mobility_product(block, wall, r_vectors, vec, eta, a, periodic_length=kwargs.get("periodic_length"),
+                                precision=precision, flags=_kw_flags(kwargs, flags))
+    f.__doc__ = doc + _DETERMINISTIC_DOC
     return f
 
 
 def _make_fused(wall, precision=FP64, doc=""):
     def f(r_vectors, force, torque, eta, a, *args, **kwargs):
         return mobility_product(UF_UT, wall, r_vectors, force, eta, a, vec_b=torque,
-                                periodic_length=kwargs.get("periodic_length"), precision=precision)
-    f.__doc__ = doc
+                                periodic_length=kwargs.get("periodic_length"), precision=precision,
+                                flags=_kw_flags(kwargs, 0))
+    f.__doc__ = doc + _DETERMINISTIC_DOC
     return f
 
 

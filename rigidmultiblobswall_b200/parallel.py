@@ -70,7 +70,8 @@ class ShardedMobility:
     the blob part of linear_operator_rigid."""
 
     def __init__(self, r_vectors, eta, a, block=_mb.UF, wall=_mb.SINGLE_WALL, periodic_length=None,
-                 precision=_mb.FP64, group=None, ranges=None, boundaries=None, local_product=None, symmetric=None):
+                 precision=_mb.FP64, group=None, ranges=None, boundaries=None, local_product=None, symmetric=None,
+                 deterministic=False):
         single = group is False or not dist.is_initialized()      # group=False: single process on purpose
         self.group = None if single else (dist.group.WORLD if group is None else group)
         self.world = 1 if single else dist.get_world_size(group)
@@ -81,9 +82,13 @@ class ShardedMobility:
         self.offset, self.count = self.ranges[self.rank]
         self.vec = ShardedVector(self.ranges, 3, self.r.device, group=self.group)
         self.eta, self.a, self.block, self.wall, self.L, self.precision = eta, a, block, wall, periodic_length, precision
+        # deterministic=True: never the pair-symmetric kernel (row kernel: fixed summation order, and its target
+        # shards re-assemble bit-exactly whatever the number of ranks)
+        if deterministic:
+            symmetric = False
         self._product = local_product or (lambda r, v, targets: _mb.mobility_product(
             self.block, self.wall, r, v, self.eta, self.a, periodic_length=self.L, precision=self.precision,
-            targets=targets))
+            targets=targets, flags=_mb.DETERMINISTIC if deterministic else 0))
 
         # Pair-symmetric schedule (UF / UT / WF / WT, wall or no wall; fp64, not periodic in z): the unordered pairs are dealt to the
         # ranks row group by row group, every rank accumulates raw sums for ALL blobs, the sums are all-reduced
@@ -176,7 +181,8 @@ class ShardedRigidSystem:
         return res
 
     def build_preconditioner(self):
-        self.PC = self.backend.BlockDiagonalPreconditioner(self.bodies, self.r_loc, self.eta, self.a, wall=self.wall)
+        make = getattr(self.backend, "block_diagonal_preconditioner", self.backend.BlockDiagonalPreconditioner)
+        self.PC = make(self.bodies, self.r_loc, self.eta, self.a, wall=self.wall)
         return self.PC
 
     # -- solves -------------------------------------------------------------------------------------------

@@ -248,12 +248,19 @@ class BlockDiagonalPreconditioner:
             eye = torch.eye(self.m, dtype=torch.float64, device=self.bodies.device).expand(self.bodies.n_bodies, -1, -1)
             self.L_inv = torch.linalg.solve_triangular(self.chol, eye, upper=False)
 
+    def _P_mult(self, w):
+        """P w = Lc^-T w"""
+        self._ensure_stoch()
+        return self._unpad((self.L_inv.transpose(1, 2) @ self._pad(w.reshape(-1)).unsqueeze(2)).squeeze(2))
+
+    def _PT_mult(self, w):
+        """P^T w = Lc^-1 w"""
+        self._ensure_stoch()
+        return self._unpad((self.L_inv @ self._pad(w.reshape(-1)).unsqueeze(2)).squeeze(2))
+
     def mobility_pc(self, w, mobility_mult):
         """y = P^T M P w with the block-diagonal P = Lc^-T; mobility_mult(v) applies the full blob mobility."""
-        self._ensure_stoch()
-        v = self._unpad((self.L_inv.transpose(1, 2) @ self._pad(w.reshape(-1)).unsqueeze(2)).squeeze(2))
-        mv = mobility_mult(v).reshape(-1)
-        return self._unpad((self.L_inv @ self._pad(mv).unsqueeze(2)).squeeze(2))
+        return self._PT_mult(mobility_mult(self._P_mult(w)).reshape(-1))
 
     def P_inv_mult(self, w):
         """y = P^-1 w = Lc w (maps the preconditioned Lanczos noise back, stochastic_forcing.py:256)."""
@@ -264,11 +271,91 @@ class BlockDiagonalPreconditioner:
         return self._unpad((self.M_inv @ self._pad(w.reshape(-1)).unsqueeze(2)).squeeze(2))
 
 
+class GroupedBlockDiagonalPreconditioner:
+    """The same preconditioner for suspensions whose bodies differ widely in size.  BlockDiagonalPreconditioner pads
+    every body to the largest one ([n_bodies, 3 nb_max, 3 nb_max] per factor): one 2,000-blob body among 1,000
+    15-blob bodies would cost 288 GB per factor and O(n_bodies nb_max^3) Cholesky work, where the reference
+    factorises each body at its own size (multi_bodies.py:766-785).  Here the bodies are bucketed by blob count
+    (a bucket spans at most a factor 1.25 in size), each bucket is one batched BlockDiagonalPreconditioner over its
+    own sub-suspension, and vectors are gathered / scattered by index."""
+
+    SPREAD = 1.25
+
+    def __init__(self, bodies, r_vectors, eta, a, wall=True):
+        self.bodies = bodies
+        dev = bodies.device
+        counts, off = bodies.counts, bodies.body_offset_host
+        ref = bodies.reference_configuration.cpu().numpy()
+        loc, quat = bodies.location.cpu().numpy(), bodies.quaternion.cpu().numpy()
+        presc = None
+        if bodies.any_prescribed:
+            pm, pv = bodies.prescribed.cpu().numpy(), bodies.prescribed_velocity.cpu().numpy()
+            presc = [pv[k] if pm[k] else None for k in range(bodies.n_bodies)]
+        r3 = r_vectors.reshape(-1, 3)
+        order = np.argsort(counts, kind="stable")
+        self.groups = []
+        k = 0
+        while k < len(order):
+            c0 = counts[order[k]]
+            j = k
+            while j < len(order) and counts[order[j]] <= self.SPREAD * c0:
+                j += 1
+            idx = np.sort(order[k:j])
+            blob_idx = np.concatenate([np.arange(off[b], off[b + 1]) for b in idx])
+            sub = RigidBodies([ref[off[b]:off[b + 1]] for b in idx], loc[idx], quat[idx], device=dev,
+                              prescribed_velocity=None if presc is None else [presc[b] for b in idx])
+            bi = torch.from_numpy(blob_idx).to(dev)
+            comp = (3 * bi.unsqueeze(1) + torch.arange(3, device=dev)).reshape(-1)      # blob-vector components
+            bodyc = (6 * torch.from_numpy(idx).to(dev).unsqueeze(1) + torch.arange(6, device=dev)).reshape(-1)
+            pc = BlockDiagonalPreconditioner(sub, r3[bi].reshape(-1).contiguous(), eta, a, wall=wall)
+            self.groups.append((pc, comp, bodyc))
+            k = j
+
+    def padded_bytes(self):
+        return sum(8 * pc.bodies.n_bodies * pc.m * pc.m for pc, _, _ in self.groups)
+
+    def __call__(self, vector):
+        n3 = 3 * self.bodies.n_blobs
+        out = torch.empty_like(vector)
+        for pc, comp, bodyc in self.groups:
+            y = pc(torch.cat([vector[comp], vector[n3 + bodyc]]))
+            out[comp] = y[:comp.numel()]
+            out[n3 + bodyc] = y[comp.numel():]
+        return out
+
+    def _blobwise(self, w, name, *extra):
+        w = w.reshape(-1)
+        out = torch.empty_like(w)
+        for pc, comp, _ in self.groups:
+            out[comp] = getattr(pc, name)(w[comp], *extra).reshape(-1)
+        return out
+
+    def mobility_pc(self, w, mobility_mult):
+        """y = P^T M P w: the block-diagonal P^T and P act bucket by bucket, M on the whole blob vector"""
+        v = self._blobwise(w, "_P_mult")
+        return self._blobwise(mobility_mult(v).reshape(-1), "_PT_mult")
+
+    def P_inv_mult(self, w):
+        return self._blobwise(w, "P_inv_mult")
+
+    def M_inv_mult(self, w):
+        return self._blobwise(w, "M_inv_mult")
+
+
+def block_diagonal_preconditioner(bodies, r_vectors, eta, a, wall=True):
+    """BlockDiagonalPreconditioner, or its bucketed form when padding every body to the largest one would more than
+    double the storage (sum over bodies of (3 nb_max)^2 against (3 nb_b)^2)."""
+    c = bodies.counts.astype(np.float64)
+    if bodies.uniform or bodies.n_bodies * float(bodies.nb_max) ** 2 <= 2.0 * float((c * c).sum()):
+        return BlockDiagonalPreconditioner(bodies, r_vectors, eta, a, wall=wall)
+    return GroupedBlockDiagonalPreconditioner(bodies, r_vectors, eta, a, wall=wall)
+
+
 def build_block_diagonal_preconditioners_det_stoch(bodies, r_vectors, Nblobs, eta, a, *args, **kwargs):
     """multi_bodies.build_block_diagonal_preconditioners_det_stoch (multi_bodies.py:480): returns
     (block_diagonal_preconditioner, mobility_pc, P_inv_mult).  kwargs: mobility_mult (callable applying the blob
     mobility; default single-wall B200 product with kwargs['periodic_length']), wall."""
-    PC = BlockDiagonalPreconditioner(bodies, r_vectors, eta, a, wall=kwargs.get("wall", True))
+    PC = block_diagonal_preconditioner(bodies, r_vectors, eta, a, wall=kwargs.get("wall", True))
     mult = kwargs.get("mobility_mult")
     if mult is None:
         L = kwargs.get("periodic_length")
@@ -280,7 +367,7 @@ def build_block_diagonal_preconditioners_det_stoch(bodies, r_vectors, Nblobs, et
 
 def build_block_diagonal_preconditioner(bodies, r_vectors, Nblobs, eta, a, *args, **kwargs):
     """Same role as multi_bodies.build_block_diagonal_preconditioner (multi_bodies.py:752): returns the callable."""
-    return BlockDiagonalPreconditioner(bodies, r_vectors, eta, a, wall=kwargs.get("wall", True))
+    return block_diagonal_preconditioner(bodies, r_vectors, eta, a, wall=kwargs.get("wall", True))
 
 
 def solve_mobility_problem(bodies, force_torque, eta, a, tolerance=1e-8, periodic_length=None, slip=None,
@@ -311,7 +398,7 @@ def solve_mobility_problem(bodies, force_torque, eta, a, tolerance=1e-8, periodi
     if float(nrm) > 0:
         rhs = rhs / nrm
     if PC is None:
-        PC = BlockDiagonalPreconditioner(bodies, r, eta, a, wall=wall)
+        PC = block_diagonal_preconditioner(bodies, r, eta, a, wall=wall)
     if mobility_vector_prod is None:
         mobility_vector_prod = (mobility.single_wall_mobility_trans_times_force_b200 if wall
                                 else mobility.no_wall_mobility_trans_times_force_b200)
@@ -348,7 +435,7 @@ def solve_resistance_problem(bodies, velocity, eta, a, tolerance=1e-8, periodic_
     if float(nrm) > 0:
         rhs = rhs / nrm
     if PC is None:
-        PC = BlockDiagonalPreconditioner(bodies, r, eta, a, wall=wall)
+        PC = block_diagonal_preconditioner(bodies, r, eta, a, wall=wall)
     if mobility_vector_prod is None:
         mobility_vector_prod = (mobility.single_wall_mobility_trans_times_force_b200 if wall
                                 else mobility.no_wall_mobility_trans_times_force_b200)
@@ -369,7 +456,7 @@ def body_mobility(bodies, eta, a, tolerance=1e-10, periodic_length=None, PC=None
     Returns N as a [6 Nbodies, 6 Nbodies] device tensor (row/column order: body-major, (U, omega) / (F, T))."""
     n6 = 6 * bodies.n_bodies
     if PC is None:
-        PC = BlockDiagonalPreconditioner(bodies, bodies.get_r_vectors(), eta, a, wall=wall)
+        PC = block_diagonal_preconditioner(bodies, bodies.get_r_vectors(), eta, a, wall=wall)
     N = torch.empty(n6, n6, dtype=torch.float64, device=bodies.device)
     e = torch.zeros(n6, dtype=torch.float64, device=bodies.device)
     for c in range(n6):

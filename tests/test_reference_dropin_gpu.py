@@ -87,3 +87,43 @@ def test_free_surface_and_radii_strings(mbod):
         assert relerr(np.asarray(u).reshape(-1), np.asarray(v).reshape(-1)) < 1e-12, ours
     # strings the reference already knows are untouched
     assert mbod.set_mobility_vector_prod("numba") is mbod.mb.single_wall_mobility_trans_times_force_numba
+
+
+def test_mixed_size_bodies_use_the_bucketed_preconditioner(mbod):
+    """Bodies of 12, 15 and 162 blobs in one suspension: the reference factorises each body at its own size
+    (multi_bodies.py:766-785); the device preconditioner buckets them by size instead of padding all to 162 blobs."""
+    import os
+    from oracle import ref_driver
+    from rigidmultiblobswall_b200 import rigid
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "rigid_golden.npz"))
+    kinds = [g["struct/boomerang_N_15"]] * 9 + [g["struct/shell_N_162"]] * 1 + [g["struct/shell_N_12"]] * 6
+    rng = np.random.default_rng(8)
+    order = rng.permutation(len(kinds))
+    cfgs = [kinds[k] for k in order]
+    nb = len(cfgs)
+    loc = np.array([[6.0 * (k % 4), 6.0 * (k // 4), 3.0 + rng.random()] for k in range(nb)])
+    quat = rng.standard_normal((nb, 4))
+    quat /= np.linalg.norm(quat, axis=1)[:, None]
+    a, eta, tol = 0.25, 1.0, 1e-8
+    FT = rng.standard_normal(6 * nb)
+    ref = ref_driver.mobility_problem(cfgs, loc, quat, FT, a, eta, tol, implementation="numba", mbod=mbod)
+    bodies = rigid.RigidBodies(cfgs, loc, quat)
+    r = bodies.get_r_vectors()
+    PC = rigid.block_diagonal_preconditioner(bodies, r, eta, a)
+    assert isinstance(PC, rigid.GroupedBlockDiagonalPreconditioner) and len(PC.groups) == 2
+    padded = rigid.BlockDiagonalPreconditioner(bodies, r, eta, a)
+    assert PC.padded_bytes() < 0.25 * 8 * nb * padded.m * padded.m
+    x = torch.from_numpy(rng.standard_normal(3 * bodies.n_blobs + 6 * nb)).cuda()
+    PC_ref = mbod.build_block_diagonal_preconditioner(ref["bodies"], [], ref["r_vectors"], ref["n_blobs"], eta, a,
+                                                      step=0, update_PC=1)
+    y_ref = PC_ref(x.cpu().numpy())
+    assert relerr(PC(x).cpu().numpy(), y_ref) < 1e-9
+    assert relerr(padded(x).cpu().numpy(), y_ref) < 1e-9
+    w = x[:3 * bodies.n_blobs]
+    assert relerr(PC.M_inv_mult(w).cpu().numpy(), padded.M_inv_mult(w).cpu().numpy()) < 1e-10
+    assert relerr(PC.P_inv_mult(w).cpu().numpy(), padded.P_inv_mult(w).cpu().numpy()) < 1e-10
+    mult = lambda v: v * 2.0
+    assert relerr(PC.mobility_pc(w, mult).cpu().numpy(), padded.mobility_pc(w, mult).cpu().numpy()) < 1e-10
+    vel, lam, its, info = rigid.solve_mobility_problem(bodies, FT, eta, a, tolerance=tol)
+    assert info == 0 and abs(its - ref["iterations"]) <= 1
+    assert relerr(vel.reshape(-1).cpu().numpy(), ref["solution"][3 * bodies.n_blobs:]) < 1e-6
