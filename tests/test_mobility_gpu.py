@@ -26,6 +26,26 @@ def relerr(x, ref):
     return np.linalg.norm(np.asarray(x) - ref) / np.linalg.norm(ref)
 
 
+def oracle_rows(block, wall, r, v, eta, a, L=None, m=192, seed=0, in_plane=False):
+    """(idx, oracle rows of M v for m RANDOM targets): self-comparison between two of our kernels is not parity, so
+    every such test also checks both against the oracle.  The product is equivariant under a permutation of the
+    blobs: the oracle's contiguous `targets` range is applied to a copy with the sampled blobs moved to the front."""
+    import oracle
+    r = (r.detach().cpu().numpy() if hasattr(r, "detach") else np.asarray(r)).reshape(-1, 3)
+    v = (v.detach().cpu().numpy() if hasattr(v, "detach") else np.asarray(v)).reshape(-1, 3)
+    n = r.shape[0]
+    rng = np.random.default_rng(seed)
+    idx = np.sort(rng.choice(n, min(m, n), replace=False))
+    perm = np.concatenate([idx, np.setdiff1d(np.arange(n), idx, assume_unique=True)])
+    ref = oracle.mobility_product(block, wall, r[perm], v[perm], eta, a, L, in_plane=in_plane, targets=(0, len(idx)))
+    return idx, ref
+
+
+def rows3(u, idx):
+    u = u.detach().cpu().numpy() if hasattr(u, "detach") else np.asarray(u)
+    return u.reshape(-1, 3)[idx].reshape(-1)
+
+
 @pytest.fixture(scope="module")
 def mb():
     from rigidmultiblobswall_b200 import mobility
@@ -230,9 +250,13 @@ def test_symmetric_large_matches_default_and_in_plane(mb):
     ref = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a)
     out = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, flags=mb.SYMMETRIC)
     assert relerr(out, ref) < 1e-13
+    idx, orc = oracle_rows("UF", "single_wall", r, f, eta, a, seed=1)
+    assert relerr(rows3(out, idx), orc) < TOL64 and relerr(rows3(ref, idx), orc) < TOL64
     ref = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, flags=mb.IN_PLANE)
     out = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, flags=mb.IN_PLANE | mb.SYMMETRIC)
     assert relerr(out, ref) < 1e-13
+    idx, orc = oracle_rows("UF", "single_wall", r, f, eta, a, seed=2, in_plane=True)
+    assert relerr(rows3(out, idx), orc) < TOL64 and relerr(rows3(ref, idx), orc) < TOL64
     # a request the symmetric kernel does not cover (target subset) silently takes the default path
     part = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a, flags=mb.SYMMETRIC, targets=(100, 300))
     assert relerr(part, ref_full := mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a)[300:1200]) < 1e-13
@@ -258,6 +282,8 @@ def test_default_selection_and_deterministic_flag(mb):
     assert torch.equal(torch.cat(parts), det)
     sym = mb.mobility_product(mb.UF, mb.SINGLE_WALL, r, f, eta, a)
     assert float(torch.linalg.norm(sym - det) / torch.linalg.norm(det)) < 1e-13
+    idx, orc = oracle_rows("UF", "single_wall", r, f, eta, a, seed=3)
+    assert relerr(rows3(det, idx), orc) < TOL64 and relerr(rows3(sym, idx), orc) < TOL64
     world = 3
     acc = sum(mb.symmetric_partial(r, f, eta, a, rank=k, world=world).clone() for k in range(world))
     # the finish step reads its arguments only: unrelated products on the same stream between the two steps
@@ -367,6 +393,8 @@ def test_symmetric_periodic_large_default_and_multi_rank(mb):
         det = mb.mobility_product(mb.UF, w, r, f, eta, a, periodic_length=L, flags=mb.DETERMINISTIC)
         sym = mb.mobility_product(mb.UF, w, r, f, eta, a, periodic_length=L)
         assert float(torch.linalg.norm(sym - det) / torch.linalg.norm(det)) < 1e-13
+        idx, orc = oracle_rows("UF", "single_wall" if w == mb.SINGLE_WALL else "no_wall", r, f, eta, a, L, seed=4)
+        assert relerr(rows3(det, idx), orc) < TOL64 and relerr(rows3(sym, idx), orc) < TOL64
         world = 3
         acc = sum(mb.symmetric_partial(r, f, eta, a, rank=k, world=world, wall=w, periodic_length=L).clone()
                   for k in range(world))
@@ -431,6 +459,8 @@ def test_symmetric_rotation_blocks_large_default_and_multi_rank(mb, blk):
         det = mb.mobility_product(b, mb.SINGLE_WALL, r, v, eta, a, periodic_length=L, flags=mb.DETERMINISTIC)
         sym = mb.mobility_product(b, mb.SINGLE_WALL, r, v, eta, a, periodic_length=L)
         assert float(torch.linalg.norm(sym - det) / torch.linalg.norm(det)) < 1e-13
+        idx, orc = oracle_rows(blk, "single_wall", r, v, eta, a, L, seed=5)
+        assert relerr(rows3(det, idx), orc) < TOL64 and relerr(rows3(sym, idx), orc) < TOL64
         world = 3
         acc = sum(mb.symmetric_partial(r, v, eta, a, rank=k, world=world, block=b, periodic_length=L).clone()
                   for k in range(world))
@@ -440,6 +470,8 @@ def test_symmetric_rotation_blocks_large_default_and_multi_rank(mb, blk):
     nw = mb.mobility_product(b, mb.NO_WALL, r, v, eta, a, flags=mb.SYMMETRIC)
     nw_det = mb.mobility_product(b, mb.NO_WALL, r, v, eta, a, flags=mb.DETERMINISTIC)
     assert float(torch.linalg.norm(nw - nw_det) / torch.linalg.norm(nw_det)) < 1e-13
+    idx, orc = oracle_rows(blk, "no_wall", r, v, eta, a, seed=6)
+    assert relerr(rows3(nw, idx), orc) < TOL64 and relerr(rows3(nw_det, idx), orc) < TOL64
 
 
 # ---- pair-symmetric kernel for the fused product u = UF f + UT t (single wall) ----
@@ -485,6 +517,9 @@ def test_symmetric_fused_large_default_and_multi_rank(mb):
         assert float(torch.linalg.norm(two - det) / torch.linalg.norm(det)) < 1e-13
         sym = mb.single_wall_mobility_trans_times_force_torque_b200(r, f, t, eta, a, periodic_length=L)   # default
         assert float(torch.linalg.norm(sym - det) / torch.linalg.norm(det)) < 1e-13
+        idx, o1 = oracle_rows("UF", "single_wall", r, f, eta, a, L, seed=7)
+        _, o2 = oracle_rows("UT", "single_wall", r, t, eta, a, L, seed=7)            # same seed: same rows
+        assert relerr(rows3(det, idx), o1 + o2) < TOL64 and relerr(rows3(sym, idx), o1 + o2) < TOL64
         world = 3
         acc = sum(mb.symmetric_partial(r, f, eta, a, rank=k, world=world, block=mb.UF_UT, vec_b=t,
                                        periodic_length=L).clone() for k in range(world))

@@ -78,6 +78,12 @@ def test_large_default_and_multi_rank(mb, blk):
         det = mb.mobility_product(b, mb.NO_WALL, r, v, eta, a, periodic_length=L, vec_b=t, flags=mb.DETERMINISTIC)
         sym = mb.mobility_product(b, mb.NO_WALL, r, v, eta, a, periodic_length=L, vec_b=t)
         assert float(torch.linalg.norm(sym - det) / torch.linalg.norm(det)) < 1e-13
+        # self-comparison is not parity: 192 random rows of both against the oracle
+        from test_mobility_gpu import oracle_rows, rows3
+        idx, orc = oracle_rows("UF" if blk == "UF_UT" else blk, "no_wall", r, v, eta, a, L, seed=9)
+        if blk == "UF_UT":
+            orc = orc + oracle_rows("UT", "no_wall", r, t, eta, a, L, seed=9)[1]
+        assert relerr(rows3(det, idx), orc) < TOL64 and relerr(rows3(sym, idx), orc) < TOL64
         world = 3
         acc = sum(mb.symmetric_partial(r, v, eta, a, rank=k, world=world, block=b, wall=mb.NO_WALL, vec_b=t,
                                        periodic_length=L).clone() for k in range(world))
