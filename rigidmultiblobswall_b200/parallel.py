@@ -82,8 +82,8 @@ class ShardedMobility:
         self.offset, self.count = self.ranges[self.rank]
         self.vec = ShardedVector(self.ranges, 3, self.r.device, group=self.group)
         self.eta, self.a, self.block, self.wall, self.L, self.precision = eta, a, block, wall, periodic_length, precision
-        # deterministic=True: never the pair-symmetric kernel (row kernel: fixed summation order, and its target
-        # shards re-assemble bit-exactly whatever the number of ranks)
+        # deterministic=True: never the pair-symmetric kernel (row kernel: fixed summation order for a given sharding,
+        # bit-reproducible run to run; different shardings agree to rounding)
         if deterministic:
             symmetric = False
         self._product = local_product or (lambda r, v, targets: _mb.mobility_product(
