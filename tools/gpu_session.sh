@@ -35,6 +35,11 @@ ncu) echo "== ncu full captures"
     [ $name = flagship ] && ncu -i /tmp/${T}_${name}_full.ncu-rep --page source --csv > gpurun_out/${T}_${name}_source.csv 2>/dev/null
   done
   echo "== launch list"; ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches.csv python bench.py --n 200000 --steps 2 --warmup 1 --no-cpu --no-extra --profiling > gpurun_out/${T}_ncu_launch.log 2>&1; echo "rc=$?";;
+multi) G=${GPUS:-8}; echo "== $G GPUs: bench (with c5 at 8), per-rank breakdown, reference arm under torchrun"
+  TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $G --master-addr 127.0.0.1 --master-port 29511"
+  timeout 900 $TR bench.py --gpus $G --steps 5 --warmup 3 > gpurun_out/${T}_bench_${G}gpu.json 2> gpurun_out/${T}_bench_${G}gpu.err; echo "rc=$?"; cut -c1-600 gpurun_out/${T}_bench_${G}gpu.json; tail -3 gpurun_out/${T}_bench_${G}gpu.err
+  timeout 300 $TR tools/rank_breakdown.py > gpurun_out/${T}_rank_breakdown_${G}gpu.json 2> gpurun_out/${T}_rank_breakdown.err; echo "rc=$?"; cat gpurun_out/${T}_rank_breakdown_${G}gpu.json
+  timeout 300 $TR bench.py --impl reference --gpus $G --steps 1 --warmup 0 --no-solve > gpurun_out/${T}_ref_${G}gpu.json 2> gpurun_out/${T}_ref_${G}gpu.err; echo "rc=$?"; cut -c1-400 gpurun_out/${T}_ref_${G}gpu.json;;
 smalln) echo "== small-N latency: this build vs the r01 source split (>= 1024 sources per CTA)"
   for so in default build_tune/split1024.so; do
     [ $so = default ] && unset RMB_LIB || export RMB_LIB=$PWD/$so
