@@ -418,6 +418,29 @@ def dense_record(n=200000):
     return rec
 
 
+def fp32_record(n=400000):
+    """The fp32 variant (north_star): single-wall UF with fp32 pair arithmetic (row kernel), its rate, the FP32 FMA
+    probe of this GPU, and 256 random rows against the fp64 oracle (bar: 1e-5)."""
+    import torch
+    import oracle
+    from rigidmultiblobswall_b200 import _lib, mobility as mb
+    r, f, a, eta = make_cloud(n)
+    rd, fd = torch.from_numpy(r).cuda().reshape(-1), torch.from_numpy(f).cuda().reshape(-1)
+    fn = lambda: mb.mobility_product(mb.UF, mb.SINGLE_WALL, rd, fd, eta, a, precision=mb.FP32)
+    fn()
+    ms, u = timed_events(fn, 3, torch)
+    idx, perm = sampled_rows(n, 256, seed=51)
+    oracle.set_threads()
+    ref = oracle.uf_wall_fast(r[perm], f[perm], eta, a, targets=(0, len(idx)))
+    got = u.reshape(-1, 3)[torch.from_numpy(idx).cuda()].reshape(-1).cpu().numpy()
+    peak32, _ = _lib.fma_peak(_lib.FP32, 200000)
+    return {"n": n, "kernel": "mf_kernel<float, UF, WALL> (one thread per target)", "pairs_per_s": float(n) * n / ms * 1e3,
+            "rel_err_256_random_rows_vs_oracle": float(np.linalg.norm(got - ref) / np.linalg.norm(ref)),
+            "fp32_fma_probe_tflops": peak32 / 1e12,
+            "ncu": "profiles/r02b_uf_f32_ncu_summary.txt: 76.3 warp instructions per pair, issue slots 88.7 % busy "
+                   "(the bound: one instruction per scheduler per clock), FMA pipe 74.4 %"}
+
+
 def c5_record(world, rank, dev, n_bodies=10000, tol=1e-6, lanczos_tol=1e-4):
     """BASELINE config 5: one Brownian step (preconditioner, Lanczos M^{1/2} z, GMRES with the random slip) for
     n_bodies shell_N_162 spheres sharded by body over the ranks.  Seconds are CUDA-event times, max over ranks."""
@@ -573,7 +596,7 @@ def run_b200(args):
     if single and not args.no_cpu:
         cpu, mb_ref = cpu_baseline_record(min(n, args.ref_sample))
 
-    solve = c3 = small = dense = None
+    solve = c3 = small = dense = fp32 = None
     if single and not args.no_solve:
         solve, _ = gmres_mobility_solve()
         if not args.no_cpu:
@@ -582,6 +605,7 @@ def run_b200(args):
         c3 = c3_record()
         small = small_n_record(mb_ref)
         dense = dense_record()
+        fp32 = fp32_record()
     c5 = None
     if world == 8 and not args.no_extra:
         c5 = c5_record(world, rank, dev)
@@ -641,7 +665,7 @@ def run_b200(args):
             "clocks": clocks,
             "parity": parity,
             "gmres_mobility_solve": solve,
-            "c3": c3, "c5": c5, "small_n": small, "dense": dense,
+            "c3": c3, "c5": c5, "small_n": small, "dense": dense, "fp32": fp32,
         }
         if traffic_note:
             line["roofline"]["traffic_note"] = traffic_note
@@ -674,7 +698,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-solve", action="store_true", help="skip the config-2 GMRES mobility solve")
-    ap.add_argument("--no-extra", action="store_true", help="skip the c3 / c5 / small_n / dense sub-records")
+    ap.add_argument("--no-extra", action="store_true", help="skip the c3 / c5 / small_n / dense / fp32 sub-records")
     ap.add_argument("--profiling", action="store_true", help="run under ncu: timings are not measurements")
     args = ap.parse_args()
     if args.impl == "reference":
