@@ -3,11 +3,11 @@ host cores at N = 1,000 / 10,000 / 100,000, next to the 
 use on the GPU box (where /root/reference does not exist).   python tools/time_numba_reference.py > profiles/<name>.json"""
 import json, os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-sys.path.insert(0, "/root/reference/mobility")
 import numpy as np
 import numba
-import mobility_numba
 import oracle
+from oracle import make_ref
+mobility_numba = make_ref.import_mobility().mobility_numba        # the staged, byte-identical copy (oracle/_ref)
 from bench import make_cloud
 
 res = {"numba_threads": numba.get_num_threads(), "oracle_threads": oracle.threads(), "cpu_count": os.cpu_count(), "rates": {}}
