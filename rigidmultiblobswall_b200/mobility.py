@@ -286,7 +286,7 @@ def symmetric_finish(r_vectors, vec, acc, eta, a, targets=None, out=None, flags=
 _DETERMINISTIC_DOC = ("\n    Extra keyword (not in the reference): deterministic=True forces the one-thread-per-target row kernel "
                       "(fixed summation order, bit-reproducible, like the reference's per-row sum).  By default products "
                       "of >= %d blobs use the pair-symmetric kernel, whose atomics make the last bits run-dependent."
-                      % 16384)
+                      % _lib.SYMMETRIC_MIN_N)
 
 
 def _kw_flags(kwargs, flags):

@@ -98,7 +98,7 @@ class ShardedMobility:
         eligible = block in (_mb.UF, _mb.UT, _mb.WF, _mb.WT) and wall in (_mb.SINGLE_WALL, _mb.NO_WALL)
         self.symmetric = (symmetric is not False and local_product is None and eligible and
                           precision == _mb.FP64 and open_z and
-                          (symmetric is True or n >= 16384))
+                          (symmetric is True or n >= _mb._lib.SYMMETRIC_MIN_N))
         self._acc = None
 
     def __call__(self, vec_local):

@@ -40,6 +40,9 @@ multi) G=${GPUS:-8}; echo "== $G GPUs: bench (with c5 at 8), per-rank breakdown,
   timeout 900 $TR bench.py --gpus $G --steps 5 --warmup 3 > gpurun_out/${T}_bench_${G}gpu.json 2> gpurun_out/${T}_bench_${G}gpu.err; echo "rc=$?"; cut -c1-600 gpurun_out/${T}_bench_${G}gpu.json; tail -3 gpurun_out/${T}_bench_${G}gpu.err
   timeout 300 $TR tools/rank_breakdown.py > gpurun_out/${T}_rank_breakdown_${G}gpu.json 2> gpurun_out/${T}_rank_breakdown.err; echo "rc=$?"; cat gpurun_out/${T}_rank_breakdown_${G}gpu.json
   timeout 300 $TR bench.py --impl reference --gpus $G --steps 1 --warmup 0 --no-solve > gpurun_out/${T}_ref_${G}gpu.json 2> gpurun_out/${T}_ref_${G}gpu.err; echo "rc=$?"; cut -c1-400 gpurun_out/${T}_ref_${G}gpu.json;;
+c2) echo "== config-2 solve breakdown; row vs symmetric kernel around the 16,384-blob threshold"
+  timeout 300 python tools/time_c2.py 2>&1 | tail -1 | tee gpurun_out/${T}_c2_breakdown.json
+  for n in 8000 12000 15000 20000 30000; do timeout 120 python tools/run_case.py UF_wall_open_f64_row,UF_wall_open_f64_sym --n $n --reps 20 --warm 3 2>&1 | tail -1; done | tee gpurun_out/${T}_row_vs_sym_small.jsonl;;
 smalln) echo "== small-N latency: this build vs the r01 source split (>= 1024 sources per CTA)"
   for so in default build_tune/split1024.so; do
     [ $so = default ] && unset RMB_LIB || export RMB_LIB=$PWD/$so
