@@ -360,6 +360,18 @@ def c3_record(n=100000):
     rec["blocks"]["UF+UT fused"] = {"ms": ms, "pairs_per_s": pairs / ms * 1e3,
                                     "rel_err_256_random_rows_vs_oracle": float(np.linalg.norm(got - ref) / np.linalg.norm(ref))}
     rec["four_blocks_seconds"] = sum(rec["blocks"][k]["ms"] for k in ("UF", "UT", "WF", "WT")) * 1e-3
+    # the caller of these blocks: the rollers' deterministic step (quaternion_integrator_rollers.py:905-979), device resident
+    from rigidmultiblobswall_b200 import rollers
+    omega, tol = np.array([0.0, 62.8, 0.0]), 1e-8
+    step = lambda: rollers.compute_deterministic_velocity_and_torque(rd, fd, omega, eta, a, periodic_length=L, tolerance=tol)
+    step()
+    ms, (v, T, its, info) = timed_events(step, 1, torch)
+    res = torch.from_numpy(np.tile(omega, n)).cuda() - mb.mobility_product(mb.WF, mb.SINGLE_WALL, rd, fd, eta, a, periodic_length=L) \
+        - mb.mobility_product(mb.WT, mb.SINGLE_WALL, rd, T, eta, a, periodic_length=L)
+    rec["deterministic_step"] = {"seconds": ms * 1e-3, "gmres_iterations": int(its), "info": int(info), "tolerance": tol,
+                                 "true_residual": float(torch.linalg.norm(res) / np.linalg.norm(np.tile(omega, n))),
+                                 "what": "solve M_rr T = omega - M_rt f (GMRES(20), no preconditioner), then v = M_tt f + M_tr T "
+                                         "in one fused pass; parity against the reference's own method: tests/test_rollers_gpu.py"}
     rec["parity_max_rel_err"] = max(b["rel_err_256_random_rows_vs_oracle"] for b in rec["blocks"].values())
     return rec
 

@@ -90,3 +90,43 @@ def numba_uf_rate(n, make_cloud, reps=1, mb_ref=None):
         mb_ref.single_wall_mobility_trans_times_force_numba(r, f, eta, a, periodic_length=L)
         best = min(best, time.perf_counter() - t0)
     return float(n) * n / best, best
+
+
+def patch_utils_gmres(utils_module=None):
+    """Third harness stub: general_application_utils.gmres passes `tol=` to SciPy (:598, :627), which
+    SciPy >= 1.14 no longer accepts.  The staged FILE is not edited; at run time the module's function is replaced by
+    the same call with `rtol=` (no preconditioner / left preconditioner branch, :596-598, the one the rollers use)."""
+    if utils_module is None:
+        make_ref.import_multi_bodies()
+        import general_application_utils as utils_module
+
+    def gmres(A, b, x0=None, tol=1e-05, restart=None, maxiter=None, xtype=None, M=None, callback=None, restrt=None,
+              PC_side="right"):
+        if M is not None and PC_side == "right":
+            raise NotImplementedError("harness stub: right-preconditioned calls go through ref_driver.gmres_right")
+        return spla.gmres(A, b, M=M, x0=x0, rtol=tol, atol=0, maxiter=maxiter, restart=restart, callback=callback,
+                          callback_type="pr_norm")
+
+    utils_module.gmres = gmres
+    return utils_module
+
+
+def rollers_integrator(mbod, r_vectors, force, omega, eta, a, L, tolerance, implementation="numba", domain="single_wall"):
+    """The reference's own QuaternionIntegratorRollers (quaternion_integrator_rollers.py:23-125) set up for
+    compute_deterministic_velocity_and_torque (:905): one single-blob body per roller, prescribed angular velocity."""
+    from quaternion_integrator.quaternion_integrator_rollers import QuaternionIntegratorRollers
+    from quaternion_integrator.quaternion import Quaternion
+    from body import body
+    patch_utils_gmres()
+    blob = np.zeros((1, 3))
+    bodies = [body.Body(np.array(x), Quaternion(np.array([1.0, 0.0, 0.0, 0.0])), blob, a) for x in np.asarray(r_vectors)]
+    integ = QuaternionIntegratorRollers(bodies, len(bodies), "deterministic_forward_euler_rollers", tolerance=tolerance,
+                                        domain=domain, mobility_vector_prod_implementation=implementation)
+    integ.eta, integ.a, integ.periodic_length = eta, a, L
+    integ.free_kinematics = "False"
+    integ.print_residual = False
+    integ.get_omega_one_roller = lambda: np.asarray(omega, dtype=np.float64)
+    f = np.asarray(force, dtype=np.float64).reshape(-1)
+    integ.calc_one_blob_forces = lambda r, blob_radius=None, blob_mass=None: f.copy()
+    integ.calc_blob_blob_forces = lambda r, blob_radius=None: np.zeros_like(f)
+    return integ
