@@ -262,6 +262,10 @@ __global__ void __launch_bounds__(TPB, RMB_MINB) mf_kernel(const __grid_constant
   }
 
   T ux = 0, uy = 0, uz = 0;
+  // fp32 variant: the pair arithmetic and the sum over ONE tile (<= 256 sources, or x 3^d images) are fp32, the
+  // running sum over tiles is fp64 -- a plain fp32 sum over 10^6 sources costs 2e-5 at N = 1M
+  // (profiles/r02j_fp32_error_vs_n.json), above the 1e-5 bar of north_star; 6 conversions/adds per tile are free
+  [[maybe_unused]] double wx = 0, wy = 0, wz = 0;
   int stage = 0;
   uint32_t phases = 0;
   for (int v = v0; v < v1; v++) {
@@ -287,11 +291,33 @@ __global__ void __launch_bounds__(TPB, RMB_MINB) mf_kernel(const __grid_constant
     const T* tp = tile[TMA ? stage : 0];
     if (diag) tile_pairs<T, BLOCK, WALL, PERIODIC, true>(tp, cnt, j0, gi, t, C, A.P, A.box, A.inva, ux, uy, uz);
     else tile_pairs<T, BLOCK, WALL, PERIODIC, false>(tp, cnt, j0, gi, t, C, A.P, A.box, A.inva, ux, uy, uz);
+    if constexpr (sizeof(T) == 4) {
+      wx += (double)ux; wy += (double)uy; wz += (double)uz;
+      ux = uy = uz = T(0);
+    }
     __syncthreads();
     if (TMA) stage ^= 1;
   }
 
   if (!valid) return;
+  if constexpr (sizeof(T) == 4) {
+    if (A.n_split == 1) {
+      // same fused epilogue as below, on the fp64 running sums
+      const SrcRec<T, NV>& me = A.src[gi];
+      double sv[3 * NV];
+#pragma unroll
+      for (int c = 0; c < 3 * NV; c++) sv[c] = (double)me.v[c];
+      self_apply<double, BLOCK, WALL>((double)t.h, sv, wx, wy, wz);
+      const double sc = A.norm * A.damp[gi];
+      A.out[3 * li] = wx * sc;
+      A.out[3 * li + 1] = wy * sc;
+      A.out[3 * li + 2] = A.in_plane ? 0.0 : wz * sc;
+    } else {
+      T* p = A.partial + ((size_t)blockIdx.y * A.n_tgt + li) * 3;
+      p[0] = T(wx); p[1] = T(wy); p[2] = T(wz);
+    }
+    return;
+  }
   if (A.n_split == 1) {
     // epilogue fused: self term, normalisation, damping
     const SrcRec<T, NV>& me = A.src[gi];

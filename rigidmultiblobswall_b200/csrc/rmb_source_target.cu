@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(TPB) st_kernel(const __grid_constant__ StArgs<
   }
 
   T ux = 0, uy = 0, uz = 0;
+  [[maybe_unused]] double wx = 0, wy = 0, wz = 0;   // fp32: fp64 running sum over tiles (see mf_kernel)
   int stage = 0;
   uint32_t phases = 0;
   for (int v = v0; v < v1; v++) {
@@ -135,19 +136,24 @@ __global__ void __launch_bounds__(TPB) st_kernel(const __grid_constant__ StArgs<
       }
       pair_st<T, WALLMODE>(A.K, t, rx, ry, rz, t.z + w[2], w[2], w[6], w[7], w[3], w[4], w[5], ux, uy, uz);
     }
+    if constexpr (sizeof(T) == 4) {
+      wx += (double)ux; wy += (double)uy; wz += (double)uz;
+      ux = uy = uz = T(0);
+    }
     __syncthreads();
     if (TMA) stage ^= 1;
   }
 
   if (!valid) return;
+  if constexpr (sizeof(T) == 8) { wx = ux; wy = uy; wz = uz; }
   if (A.n_split == 1) {
     const double sc = A.norm * Bt;
-    A.out[3 * li] = (double)ux * sc;
-    A.out[3 * li + 1] = (double)uy * sc;
-    A.out[3 * li + 2] = (double)uz * sc;
+    A.out[3 * li] = wx * sc;
+    A.out[3 * li + 1] = wy * sc;
+    A.out[3 * li + 2] = wz * sc;
   } else {
     T* p = A.partial + ((size_t)blockIdx.y * A.n_trg + li) * 3;
-    p[0] = ux; p[1] = uy; p[2] = uz;
+    p[0] = T(wx); p[1] = T(wy); p[2] = T(wz);
   }
 }
 

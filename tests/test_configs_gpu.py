@@ -93,6 +93,10 @@ def test_c4_one_million_blobs_1000_random_targets_against_the_oracle():
     rd, fd = torch.from_numpy(r).cuda().reshape(-1), torch.from_numpy(f).cuda().reshape(-1)
     u = mb.single_wall_mobility_trans_times_force_b200(rd, fd, eta, a)
     assert relerr(rows3(u, idx), ref) < 1e-12
+    # the fp32 variant at this size: fp32 pair arithmetic, fp64 running sum over the source tiles (north_star: 1e-5;
+    # a plain fp32 sum over 10^6 sources measures 2e-5, profiles/r02j_fp32_error_vs_n.json)
+    u32 = mb.single_wall_mobility_trans_times_force_b200_fp32(rd, fd, eta, a)
+    assert relerr(rows3(u32, idx), ref) < 1e-5
     # size-independent properties at full size: the symmetry of M (f2 . M f1 = f1 . M f2) and linearity
     f2 = torch.from_numpy(np.random.default_rng(5).standard_normal(3 * n)).cuda()
     u2 = mb.single_wall_mobility_trans_times_force_b200(rd, f2, eta, a)
