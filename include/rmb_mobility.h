@@ -165,6 +165,29 @@ int rmb_mobility_source_target(int wall, int precision, int flags, long n_target
                                void *stream);
 
 /*
+ * Allocation-free variant of rmb_mobility_product.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments and result as rmb_mobility_product minus the workspace:
+ * the scratch (packed records, damping factors, partial sums / pair-symmetric accumulator) lives in a file-scope
+ * `static __device__` array of rmb_static_workspace_max() = 64 MiB that every GPU which loads the library holds until
+ * the process exits.  The call performs no cudaMalloc / cudaFree and calls no allocating library routine; inputs and
+ * the output are the caller's.
+ *   limit    products whose rmb_workspace_bytes(...) exceeds 64 MiB (about 450,000 blobs for an fp64 single-vector
+ *            block, 330,000 for RMB_UF_UT; 80 / 112 bytes per blob plus up to 27 MB of partial sums) are rejected with RMB_E_WORKSPACE and a message in rmb_last_error()
+ *   sharing  every call on a device uses the SAME array, which keeps the last call's contents; whatever must start
+ *            at zero is cleared by the call itself on `stream`.  Calls that overlap on the GPU (different streams,
+ *            or two host threads) race on it: serialise them, or give the concurrent ones their own workspace
+ *            through rmb_mobility_product.
+ *   set-up   the first call on a device resolves the array's device address (cudaGetSymbolAddress, that device
+ *            current); make that first call outside stream capture.
+ */
+size_t rmb_static_workspace_max(void);
+int rmb_mobility_product_static(int block, int wall, int precision, int flags,
+                                long n_targets, long n_sources, long target_offset,
+                                const double *r_sources, const double *vec_a, const double *vec_b,
+                                double eta, double a, const double *L, double *out, void *stream);
+
+/*
  * FP64 (precision = RMB_FP64) or FP32 FMA-pipe peak probe: runs `iters`
  * dependent-chain-free FMAs per thread on a full grid and returns the
  * measured rate in FLOP/s through *flops (host).  Synchronises.  Used by

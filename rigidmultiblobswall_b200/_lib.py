@@ -47,6 +47,12 @@ def load():
                                          ctypes.c_long, ctypes.c_long, ctypes.c_long,
                                          c_dp, c_dp, c_dp, ctypes.c_double, ctypes.c_double,
                                          ctypes.POINTER(ctypes.c_double), c_dp, c_dp, ctypes.c_size_t, c_dp]
+    lib.rmb_static_workspace_max.restype = ctypes.c_size_t
+    lib.rmb_mobility_product_static.restype = ctypes.c_int
+    lib.rmb_mobility_product_static.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                                ctypes.c_long, ctypes.c_long, ctypes.c_long,
+                                                c_dp, c_dp, c_dp, ctypes.c_double, ctypes.c_double,
+                                                ctypes.POINTER(ctypes.c_double), c_dp, c_dp]
     lib.rmb_source_target_workspace_bytes.restype = ctypes.c_size_t
     lib.rmb_source_target_workspace_bytes.argtypes = [ctypes.c_int, ctypes.c_long, ctypes.c_long,
                                                       ctypes.POINTER(ctypes.c_double)]

@@ -1070,6 +1070,59 @@ int rmb_symmetric_finish(int block, int wall, int flags, long n, long target_off
   return sym_finish(c, acc);
 }
 
+// ---- allocation-free variant (no counterpart in the reference) ----
+// Scratch of rmb_mobility_product_static: ONE file-scope device array per GPU that loads the library, held until the
+// process exits.  Host code must not use the NAME as a pointer (it is a host-side stand-in): the device address is
+// fetched once per device with cudaGetSymbolAddress, with that device current, and cached.
+#define RMB_STATIC_WORKSPACE_BYTES (64u << 20)
+static __device__ __align__(256) unsigned char g_static_workspace[RMB_STATIC_WORKSPACE_BYTES];
+static void* g_static_workspace_addr[64] = {nullptr};   // per device ordinal
+
+static int static_workspace(void** ws)
+{
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail_cuda(e, "rmb_mobility_product_static: cudaGetDevice");
+  if (dev < 0 || dev >= 64) return fail(RMB_E_ARG, "rmb_mobility_product_static: device ordinal beyond 63");
+  if (!g_static_workspace_addr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_workspace);
+    if (e != cudaSuccess || !p) return fail_cuda(e, "rmb_mobility_product_static: cudaGetSymbolAddress");
+    g_static_workspace_addr[dev] = p;
+  }
+  *ws = g_static_workspace_addr[dev];
+  return 0;
+}
+
+size_t rmb_static_workspace_max(void) { return RMB_STATIC_WORKSPACE_BYTES; }
+
+int rmb_mobility_product_static(int block, int wall, int precision, int flags, long n_targets, long n_sources,
+                                long target_offset, const double* r_sources, const double* vec_a, const double* vec_b,
+                                double eta, double a, const double* L, double* out, void* stream)
+{
+  if (block < 0 || block > RMB_UF_UT) return fail(RMB_E_ARG, "block must be RMB_UF..RMB_UF_UT");
+  if (precision != RMB_FP64 && precision != RMB_FP32) return fail(RMB_E_ARG, "precision must be 0 or 1");
+  if (n_targets < 0 || n_sources < 0) return fail(RMB_E_ARG, "negative size");
+  if (n_targets == 0 || n_sources == 0) return 0;
+  Plan p;
+  const int rc = make_plan(block, precision, n_targets, n_sources, L, p);
+  if (rc != 0) return rc;
+  if (p.total > RMB_STATIC_WORKSPACE_BYTES) {
+    snprintf(g_err, sizeof(g_err),
+             "rmb_mobility_product_static: this product needs %zu bytes of scratch, the static array holds %u "
+             "(about 450,000 blobs for an fp64 single-vector block): use rmb_mobility_product with a caller-owned workspace",
+             p.total, (unsigned)RMB_STATIC_WORKSPACE_BYTES);
+    return RMB_E_WORKSPACE;
+  }
+  void* ws = nullptr;
+  const int rs = static_workspace(&ws);
+  if (rs != 0) return rs;
+  // everything that must start at zero is cleared by the product itself (the pair-symmetric accumulator by a
+  // cudaMemsetAsync on `stream`; records, damping factors and partial sums are fully overwritten)
+  return rmb_mobility_product(block, wall, precision, flags, n_targets, n_sources, target_offset, r_sources, vec_a,
+                              vec_b, eta, a, L, out, ws, RMB_STATIC_WORKSPACE_BYTES, stream);
+}
+
 int rmb_fma_peak(int precision, int iters, double* flops, double* elapsed_ms)
 {
   const int sms = sm_count();
