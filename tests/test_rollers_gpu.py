@@ -58,3 +58,35 @@ def test_deterministic_velocity_and_torque(mbod, domain, periodic):
     v2, T2, its2, _ = rollers.compute_deterministic_velocity_and_torque(r, f, omega, eta, a, periodic_length=L,
                                                                        domain=domain, torque=T_ref)
     assert its2 == 0 and relerr(v2, v_ref) < 1e-7
+
+
+@pytest.mark.parametrize("free_kinematics", [False, True])
+def test_stochastic_velocity(mbod, free_kinematics):
+    """compute_stochastic_velocity (:1082-1200) with the same Gaussian draws as the reference takes from np.random:
+    Lanczos on the 6N grand mobility, random-finite-difference divergences, GMRES for the stochastic torque."""
+    from oracle import ref_driver
+    from rigidmultiblobswall_b200 import rollers
+    n, dt, kT, tol = 1000, 0.01, 0.0041, 1e-8
+    r, f, _, a, eta, L = bench.make_c3(n)
+    ref = ref_driver.rollers_integrator(mbod, r, f, np.zeros(3), eta, a, L, tol, implementation="numba")
+    ref.kT, ref.rf_delta = kT, 1e-3
+    ref.free_kinematics = "True" if free_kinematics else "False"
+    np.random.seed(77)
+    v_ref = ref.compute_stochastic_velocity(dt)
+    np.random.seed(77)
+    z, dx = np.random.randn(6 * n), np.random.randn(3 * n)          # the reference's two draws, in its order
+    v, it_l, its = rollers.compute_stochastic_velocity(r, dt, kT, eta, a, periodic_length=L, tolerance=tol, rf_delta=1e-3,
+                                                       free_kinematics=free_kinematics, z=z, dx_stoch=dx)
+    assert abs(it_l - ref.stoch_iterations_count) <= 1
+    assert free_kinematics or abs(its - ref.det_iterations_count) <= 1
+    # Lanczos at tolerance 1e-8 and a finite difference of two O(1) products divided by rf_delta a = 1e-3
+    assert relerr(v, v_ref) < 1e-5
+    # the grand mobility itself against the reference's four numba blocks: rounding
+    x = np.random.randn(6 * n)
+    got = rollers.grand_mobility_product(torch.from_numpy(r).cuda().reshape(-1), torch.from_numpy(x).cuda(), eta, a, L)
+    want = np.concatenate([
+        ref.mobility_trans_times_force(r, x[:3 * n], eta, a, periodic_length=L)
+        + ref.mobility_trans_times_torque(r, x[3 * n:], eta, a, periodic_length=L),
+        ref.mobility_rot_times_force(r, x[:3 * n], eta, a, periodic_length=L)
+        + ref.mobility_rot_times_torque(r, x[3 * n:], eta, a, periodic_length=L)])
+    assert relerr(got, want) < 1e-12
