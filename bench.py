@@ -431,8 +431,9 @@ def dense_record(n=200000):
 
 
 def fp32_record(n=400000):
-    """The fp32 variant (north_star): single-wall UF with fp32 pair arithmetic (row kernel), its rate, the FP32 FMA
-    probe of this GPU, and 256 random rows against the fp64 oracle (bar: 1e-5)."""
+    """The fp32 variant (north_star): single-wall UF with fp32 pair arithmetic (pair-symmetric kernel by default, row
+    kernel with RMB_DETERMINISTIC), their rates, the FP32 FMA probe of this GPU, and 256 random rows against the fp64
+    oracle (bar: 1e-5)."""
     import torch
     import oracle
     from rigidmultiblobswall_b200 import _lib, mobility as mb
@@ -446,11 +447,15 @@ def fp32_record(n=400000):
     ref = oracle.uf_wall_fast(r[perm], f[perm], eta, a, targets=(0, len(idx)))
     got = u.reshape(-1, 3)[torch.from_numpy(idx).cuda()].reshape(-1).cpu().numpy()
     peak32, _ = _lib.fma_peak(_lib.FP32, 200000)
-    return {"n": n, "kernel": "mf_kernel<float, UF, WALL> (one thread per target)", "pairs_per_s": float(n) * n / ms * 1e3,
+    row = lambda: mb.mobility_product(mb.UF, mb.SINGLE_WALL, rd, fd, eta, a, precision=mb.FP32, flags=mb.DETERMINISTIC)
+    row()
+    ms_row, _ = timed_events(row, 3, torch)
+    return {"n": n, "kernel": "sym_kernel<UF, ..., float> (fp32 pair arithmetic, every unordered pair once, fp64 sums)",
+            "pairs_per_s": float(n) * n / ms * 1e3, "row_kernel_pairs_per_s": float(n) * n / ms_row * 1e3,
             "rel_err_256_random_rows_vs_oracle": float(np.linalg.norm(got - ref) / np.linalg.norm(ref)),
             "fp32_fma_probe_tflops": peak32 / 1e12,
-            "ncu": "profiles/r02b_uf_f32_ncu_summary.txt: 76.3 warp instructions per pair, issue slots 88.7 % busy "
-                   "(the bound: one instruction per scheduler per clock), FMA pipe 74.4 %"}
+            "ncu": "row kernel, profiles/r02b_uf_f32_ncu_summary.txt: 76.3 warp instructions per pair, issue slots "
+                   "88.7 % busy (the bound: one instruction per scheduler per clock), FMA pipe 74.4 %"}
 
 
 def c5_record(world, rank, dev, n_bodies=10000, tol=1e-6, lanczos_tol=1e-4):

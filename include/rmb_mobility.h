@@ -56,9 +56,10 @@ extern "C" {
 /* flags */
 #define RMB_IN_PLANE 1    /* in_plane_* (mobility.py:255,454,1166,1235): z column and row zero */
 #define RMB_NO_TMA 2      /* stage source tiles with plain loads instead of cp.async.bulk (debug) */
-#define RMB_SYMMETRIC 4   /* evaluate every unordered pair once and update both blobs.  Exists for fp64, n_targets ==
+#define RMB_SYMMETRIC 4   /* evaluate every unordered pair once and update both blobs.  Exists for fp64 and fp32 (fp32 pair
+                             arithmetic; the sums are fp64: 32 partners at a time in fp32, then fp64 registers / atomics), n_targets ==
                              n_sources, L[2] <= 0 (open or pseudo-periodic in x / y), blocks RMB_UF / RMB_UT / RMB_WF /
-                             RMB_WT / RMB_UF_UT with RMB_SINGLE_WALL or RMB_NO_WALL; any other call (fp32, free
+                             RMB_WT / RMB_UF_UT with RMB_SINGLE_WALL or RMB_NO_WALL; any other call (free
                              surface, target shards, periodic z) ignores the flag and takes the row kernel.  Sums are accumulated with atomics: results agree with
                              the row kernel to rounding, but are not bit-reproducible run to run.  Without this
                              flag the symmetric kernel is still chosen for eligible calls with

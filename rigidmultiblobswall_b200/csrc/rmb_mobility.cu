@@ -381,8 +381,9 @@ __global__ void finish_kernel(const MfArgs<T, (BLOCK == UF_UT) ? 2 : 1> A)
 // Sums are accumulated with atomics in acc[n_pad][3]; sym_finish_kernel adds the
 // self term, the normalisation and the damping.  Padding records (zero force) are handled by the TAIL
 // instantiations: a pair with a padding blob is given a finite dummy geometry.
-struct SymArgs {
-  const double* src;              // n_tiles * TILE records of W words {x, y, z, v[3 NV], pad}; padding = zero vectors (see TAIL)
+template <typename T>
+struct SymArgsT {
+  const T* src;                   // n_tiles * TILE records of W words {x, y, z, v[3 NV], pad}; padding = zero vectors (see TAIL)
   double* acc;                    // [n_tiles * TILE][3], zeroed before the launch
   long n;                         // real blobs; records [n, n_tiles * TILE) are zero-force padding
   int n_tiles;
@@ -391,23 +392,26 @@ struct SymArgs {
   int pad_[3];                    // keeps K at an offset = 8 mod 16 in the parameter bank: with K 16-byte aligned nvcc 12.9
                                   // re-loads one more constant pair inside the pair loop (126 instead of 125 instructions;
                                   // measured 335.6 vs 338.3 G pairs/s, profiles/r02c_item_decode_ab.jsonl)
-  UfCtx<double> K;
+  UfCtx<T> K;
   // PER instantiations only (pseudo-periodic in x and/or y; records then hold unscaled positions)
-  Periodic<double> P;
-  BoxTable<double> box;
-  double inva;
+  Periodic<T> P;
+  BoxTable<T> box;
+  T inva;
 };
+typedef SymArgsT<double> SymArgs;
 
 // Registers of one lane: NT blobs, one from each of the warp's NT consecutive blocks.
-template <int NT, int NV = 1>
+// (T = float: fp32 pair arithmetic; positions and vectors are fp32, the sums u stay fp64)
+template <typename T, int NT, int NV = 1>
 struct SymLane {
-  double x[NT], y[NT], h[NT], h2[NT], h4[NT], f[NT][3 * NV], u[NT][3];
+  T x[NT], y[NT], h[NT], h2[NT], h4[NT], f[NT][3 * NV];
+  double u[NT][3];
 };
 
 // vectors per blob and record words of a block (UF_UT: force and torque / a)
-template <int BLOCK> struct SymRec {
+template <int BLOCK, typename T = double> struct SymRec {
   static constexpr int NV = (BLOCK == UF_UT) ? 2 : 1;
-  static constexpr int W = RecWords<double, NV>::value;
+  static constexpr int W = RecWords<T, NV>::value;
 };
 
 // One block J against the lane's blobs k in [K0, K0 + NK): 32 rotation steps, both directions, then the
@@ -418,12 +422,10 @@ template <int BLOCK> struct SymRec {
 // looped innermost; box b seen from i is box -b seen from j (the wrap is odd), so one evaluation with (r, -r)
 // serves both directions and the sum over b covers all boxes of both.
 // One unordered pair of block BLOCK: u_i += M_ij v_j and (BOTH) u_j += M_ji v_i from shared factors (pair_math.cuh).
-template <int BLOCK, bool WALL, bool BOTH>
-__device__ __forceinline__ void sym_pair(double rx, double ry, double rz, double Rz, double hi, double hj, double hi2,
-                                         double hi4, const UfCtx<double>& C, const double* vi, const double* vj,
-                                         bool any_near, double r2, double* ui, double* uj)
+template <typename T, int BLOCK, bool WALL, bool BOTH>
+__device__ __forceinline__ void sym_pair(T rx, T ry, T rz, T Rz, T hi, T hj, T hi2, T hi4, const UfCtx<T>& C,
+                                         const T* vi, const T* vj, bool any_near, T r2, T* ui, T* uj)
 {
-  typedef double T;
   if (BLOCK == UF) {
     if (WALL) pair_uf_wall_sym<T, BOTH>(rx, ry, rz, Rz, hi, hj, hi2, hi4, C, vi, vj, any_near, r2, ui, uj);
     else pair_uf_free_sym<T, BOTH>(rx, ry, rz, C, vi, vj, any_near, r2, ui, uj);
@@ -448,14 +450,14 @@ __device__ __forceinline__ void sym_pair(double rx, double ry, double rz, double
   }
 }
 
-template <bool PER>
-__device__ __forceinline__ void sym_geometry(const SymArgs& A, double xi, double yi, double hi, const double* w,
-                                             double& rx, double& ry, double& rz, double& hj)
+template <typename T, bool PER>
+__device__ __forceinline__ void sym_geometry(const SymArgsT<T>& A, T xi, T yi, T hi, const T* w, T& rx, T& ry, T& rz,
+                                             T& hj)
 {
   rx = xi - w[0]; ry = yi - w[1];
   if (PER) {
-    if (A.P.per[0]) rx = wrap_shift(rx, A.P.L[0], A.P.invL[0], 0.0);
-    if (A.P.per[1]) ry = wrap_shift(ry, A.P.L[1], A.P.invL[1], 0.0);
+    if (A.P.per[0]) rx = wrap_shift(rx, A.P.L[0], A.P.invL[0], T(0));
+    if (A.P.per[1]) ry = wrap_shift(ry, A.P.L[1], A.P.invL[1], T(0));
     rx *= A.inva; ry *= A.inva;
     hj = w[2] * A.inva;
   } else {
@@ -468,16 +470,23 @@ __device__ __forceinline__ void sym_geometry(const SymArgs& A, double xi, double
 // since after the minimum-image wrap only the central box can hold an overlapping pair -- was measured at 348-360
 // against 356-358 G pairs/s for this loop, profiles/r02a_per_far_boxes_ab.jsonl: the per-box vote + branch is not
 // what bounds the kernel, and the variant was dropped.)
-template <int BLOCK, int NT, int K0, int NK, bool TAIL, bool WALL, bool PER>
-__device__ __forceinline__ void sym_block(const double* __restrict__ blk, int lane,
-                                          SymLane<NT, SymRec<BLOCK>::NV>& L, const SymArgs& A,
+// T = float: the pair arithmetic, the travelling accumulator aj (32 terms) and this block's contribution to u_i
+// (32 terms x boxes) are fp32; they are added to the fp64 sums (registers / global atomics) once per block.
+template <typename T, int BLOCK, int NT, int K0, int NK, bool TAIL, bool WALL, bool PER>
+__device__ __forceinline__ void sym_block(const T* __restrict__ blk, int lane,
+                                          SymLane<T, NT, SymRec<BLOCK, T>::NV>& L, const SymArgsT<T>& A,
                                           double* __restrict__ acc_j, long i0, long j0)
 {
-  typedef double T;
-  constexpr int W = SymRec<BLOCK>::W;
+  constexpr int W = SymRec<BLOCK, T>::W;
+  constexpr bool F32 = sizeof(T) == 4;
   const UfCtx<T>& C = A.K;
   const long n = A.n;
   T aj[3] = {0, 0, 0};
+  [[maybe_unused]] T ul[NT][3];                 // fp32 only: block-local part of u_i
+  if constexpr (F32) {
+#pragma unroll
+    for (int k = 0; k < NT; k++) ul[k][0] = ul[k][1] = ul[k][2] = T(0);
+  }
   int jl = lane;
   const int from = (lane + 1) & 31;
   constexpr int SU = RMB_SYM_UNROLL;
@@ -489,14 +498,15 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
     for (int k = K0; k < K0 + NK; k++) {
       T rx, ry, rz, hj;
       T hi = L.h[k], hi2 = L.h2[k], hi4 = L.h4[k];
-      sym_geometry<PER>(A, L.x[k], L.y[k], hi, w, rx, ry, rz, hj);
+      sym_geometry<T, PER>(A, L.x[k], L.y[k], hi, w, rx, ry, rz, hj);
       if (TAIL && (j0 + jl >= n || i0 + 32 * k + lane >= n)) {   // rz = 3: no xy image shift can bring r to 0
         rx = T(PER ? 0 : 3); ry = T(0); rz = T(PER ? 3 : 0); hi = T(2); hj = T(2); hi2 = T(4); hi4 = T(8);
       }
       if (!PER) {
         const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
         const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-        sym_pair<BLOCK, WALL, true>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
+        if constexpr (F32) sym_pair<T, BLOCK, WALL, true>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, ul[k], aj);
+        else sym_pair<T, BLOCK, WALL, true>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
       } else {
         const T Rz = hi + hj, rz2 = rz * rz;
 #pragma unroll 1
@@ -504,7 +514,8 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
           const T bx = rx + A.box.s[b][0], by = ry + A.box.s[b][1];
           const T r2 = RMB_FMA(by, by, RMB_FMA(bx, bx, rz2));
           const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-          sym_pair<BLOCK, WALL, true>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
+          if constexpr (F32) sym_pair<T, BLOCK, WALL, true>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, ul[k], aj);
+          else sym_pair<T, BLOCK, WALL, true>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
         }
       }
     }
@@ -514,19 +525,26 @@ __device__ __forceinline__ void sym_block(const double* __restrict__ blk, int la
     aj[2] = __shfl_sync(0xffffffffu, aj[2], from);
     jl = (jl + 1) & 31;
   }
-  atomicAdd(acc_j + 3 * lane, aj[0]); atomicAdd(acc_j + 3 * lane + 1, aj[1]); atomicAdd(acc_j + 3 * lane + 2, aj[2]);
+  if constexpr (F32) {
+#pragma unroll
+    for (int k = K0; k < K0 + NK; k++) { L.u[k][0] += (double)ul[k][0]; L.u[k][1] += (double)ul[k][1]; L.u[k][2] += (double)ul[k][2]; }
+    atomicAdd(acc_j + 3 * lane, (double)aj[0]); atomicAdd(acc_j + 3 * lane + 1, (double)aj[1]); atomicAdd(acc_j + 3 * lane + 2, (double)aj[2]);
+  } else {
+    atomicAdd(acc_j + 3 * lane, aj[0]); atomicAdd(acc_j + 3 * lane + 1, aj[1]); atomicAdd(acc_j + 3 * lane + 2, aj[2]);
+  }
 }
 
 // Diagonal block (J == the block of blob k): ordered pairs (l, (l + s) & 31), s = 1..31, one direction.
 // PER: also s = 0, the blob's own images in the non-central boxes.
-template <int BLOCK, int NT, bool TAIL, bool WALL, bool PER>
-__device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lane, SymLane<NT, SymRec<BLOCK>::NV>& L, int k,
-                                         const SymArgs& A, long i0)
+template <typename T, int BLOCK, int NT, bool TAIL, bool WALL, bool PER>
+__device__ __forceinline__ void sym_diag(const T* __restrict__ blk, int lane, SymLane<T, NT, SymRec<BLOCK, T>::NV>& L, int k,
+                                         const SymArgsT<T>& A, long i0)
 {
-  typedef double T;
-  constexpr int W = SymRec<BLOCK>::W;
+  constexpr int W = SymRec<BLOCK, T>::W;
+  constexpr bool F32 = sizeof(T) == 4;
   const UfCtx<T>& C = A.K;
   const long n = A.n;
+  [[maybe_unused]] T ul[3] = {T(0), T(0), T(0)};   // fp32 only: this block's part of u_i
 #pragma unroll 2
   for (int s = PER ? 0 : 1; s < 32; s++) {
     T w[W];
@@ -534,14 +552,15 @@ __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lan
     load_rec<W>(blk + jl * W, w);
     T rx, ry, rz, hj;
     T hi = L.h[k], hi2 = L.h2[k], hi4 = L.h4[k];
-    sym_geometry<PER>(A, L.x[k], L.y[k], hi, w, rx, ry, rz, hj);
+    sym_geometry<T, PER>(A, L.x[k], L.y[k], hi, w, rx, ry, rz, hj);
     if (TAIL && (i0 + jl >= n || i0 + lane >= n)) {
       rx = T(PER ? 0 : 3); ry = T(0); rz = T(PER ? 3 : 0); hi = T(2); hj = T(2); hi2 = T(4); hi4 = T(8);
     }
     if (!PER) {
       const T r2 = RMB_FMA(rz, rz, RMB_FMA(ry, ry, rx * rx));
       const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-      sym_pair<BLOCK, WALL, false>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
+      if constexpr (F32) sym_pair<T, BLOCK, WALL, false>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, ul, ul);
+      else sym_pair<T, BLOCK, WALL, false>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
     } else {
       const T Rz = hi + hj, rz2 = rz * rz;
 #pragma unroll 1
@@ -550,17 +569,18 @@ __device__ __forceinline__ void sym_diag(const double* __restrict__ blk, int lan
         const T bx = rx + A.box.s[b][0], by = ry + A.box.s[b][1];
         const T r2 = RMB_FMA(by, by, RMB_FMA(bx, bx, rz2));
         const bool any_near = __any_sync(0xffffffffu, lt4(r2));
-        sym_pair<BLOCK, WALL, false>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
+        if constexpr (F32) sym_pair<T, BLOCK, WALL, false>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, ul, ul);
+        else sym_pair<T, BLOCK, WALL, false>(bx, by, rz, Rz, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], L.u[k]);
       }
     }
   }
+  if constexpr (F32) { L.u[k][0] += (double)ul[0]; L.u[k][1] += (double)ul[1]; L.u[k][2] += (double)ul[2]; }
 }
 
-template <int BLOCK, bool TMA, int NT, bool WALL, bool PER>
-__global__ void __launch_bounds__(TPB, RMB_SYM_MINB(BLOCK)) sym_kernel(const __grid_constant__ SymArgs A)
+template <int BLOCK, bool TMA, int NT, bool WALL, bool PER, typename T = double>
+__global__ void __launch_bounds__(TPB, RMB_SYM_MINB(BLOCK)) sym_kernel(const __grid_constant__ SymArgsT<T> A)
 {
-  typedef double T;
-  constexpr int W = SymRec<BLOCK>::W;
+  constexpr int W = SymRec<BLOCK, T>::W;
   constexpr uint32_t TILE_BYTES = TILE * W * sizeof(T);
   constexpr int ROW = TPB * NT;                            // blobs of one row group (CTA)
   __shared__ alignas(128) T tile[TMA ? STAGES : 1][TILE * W];
@@ -582,14 +602,14 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB(BLOCK)) sym_kernel(const __g
   const int g = (int)item.g;
   const long I0 = ((long)g * (TPB / 32) + warp) * NT;      // this warp's first block of 32
 
-  constexpr int NV = SymRec<BLOCK>::NV;
+  constexpr int NV = SymRec<BLOCK, T>::NV;
   const T* srcw = A.src;
-  SymLane<NT, NV> L;
+  SymLane<T, NT, NV> L;
 #pragma unroll
   for (int k = 0; k < NT; k++) {
     const T* me = srcw + ((I0 + k) * 32 + lane) * W;
     L.x[k] = me[0]; L.y[k] = me[1]; L.h[k] = PER ? me[2] * A.inva : me[2];
-    L.h2[k] = 2.0 * L.h[k]; L.h4[k] = 4.0 * L.h[k];
+    L.h2[k] = T(2.0) * L.h[k]; L.h4[k] = T(4.0) * L.h[k];
 #pragma unroll
     for (int c = 0; c < 3 * NV; c++) L.f[k][c] = me[3 + c];
 #pragma unroll
@@ -634,14 +654,14 @@ __global__ void __launch_bounds__(TPB, RMB_SYM_MINB(BLOCK)) sym_kernel(const __g
       const long i0 = I0 * 32, j0 = J * 32;
       const bool tail = (j0 + 32 > A.n) || (i0 + 32 * NT > A.n);   // warp-uniform, true for the last blocks only
       if (sym_block_case(I0 + NT - 1, J) == 2) {           // the hot path: all NT blobs of the lane meet block J
-        if (!tail) sym_block<BLOCK, NT, 0, NT, false, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
-        else sym_block<BLOCK, NT, 0, NT, true, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
+        if (!tail) sym_block<T, BLOCK, NT, 0, NT, false, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
+        else sym_block<T, BLOCK, NT, 0, NT, true, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
       } else if (sym_block_case(I0, J) == 1) {             // J == I0 (for NT == 2 the second blob skips: J < I0 + 1)
-        if (!tail) sym_diag<BLOCK, NT, false, WALL, PER>(blk, lane, L, 0, A, i0);
-        else sym_diag<BLOCK, NT, true, WALL, PER>(blk, lane, L, 0, A, i0);
+        if (!tail) sym_diag<T, BLOCK, NT, false, WALL, PER>(blk, lane, L, 0, A, i0);
+        else sym_diag<T, BLOCK, NT, true, WALL, PER>(blk, lane, L, 0, A, i0);
       } else {                                             // NT == 2, J == I0 + 1
-        sym_block<BLOCK, NT, 0, 1, true, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
-        sym_diag<BLOCK, NT, true, WALL, PER>(blk, lane, L, NT - 1, A, i0 + 32 * (NT - 1));
+        sym_block<T, BLOCK, NT, 0, 1, true, WALL, PER>(blk, lane, L, A, acc_j, i0, j0);
+        sym_diag<T, BLOCK, NT, true, WALL, PER>(blk, lane, L, NT - 1, A, i0 + 32 * (NT - 1));
       }
     }
     __syncthreads();
@@ -738,7 +758,7 @@ int make_plan(int block, int precision, long n_tgt, long n_src, const double* L,
   p.total = p.off_partial + (p.n_split > 1 ? (size_t)p.n_split * n_tgt * 3 * word : 0);
   // accumulators of the pair-symmetric kernel (fp64, every blob a target; see use_symmetric)
   p.off_acc = align_up(p.total, 256);
-  if (block >= RMB_UF && block <= RMB_UF_UT && precision == RMB_FP64 && n_tgt == n_src)
+  if (block >= RMB_UF && block <= RMB_UF_UT && n_tgt == n_src)      // fp64 sums for the fp32 pair arithmetic too
     p.total = p.off_acc + (size_t)p.n_tiles * TILE * 3 * sizeof(double);
   return 0;
 }
@@ -749,7 +769,7 @@ int make_plan(int block, int precision, long n_tgt, long n_src, const double* L,
 bool use_symmetric(int block, int wall, int precision, int flags, long n_tgt, long n_src, const double* L)
 {
   const bool blk = block >= RMB_UF && block <= RMB_UF_UT && (wall == RMB_SINGLE_WALL || wall == RMB_NO_WALL);
-  const bool ok = blk && precision == RMB_FP64 &&
+  const bool ok = blk && (precision == RMB_FP64 || precision == RMB_FP32) &&
                   !(L && L[2] > 0) && n_tgt == n_src && TILE % (TPB * RMB_SYM_NT) == 0;
   const bool want = (flags & RMB_SYMMETRIC) || (!(flags & RMB_DETERMINISTIC) && n_src >= RMB_SYMMETRIC_MIN_N);
   return ok && want;
@@ -810,8 +830,77 @@ int launch(const Call& c)
 
 // Pair-symmetric path: every block, fp64, wall or no wall, not periodic in z, every blob a target.
 // Step 1: records + raw pair sums of the row groups row_first, row_first + row_stride, ... into acc.
+// fp32 pair arithmetic (precision = RMB_FP32): same schedule and the same fp64 accumulator, records and kernel in float.
+int sym_partial_f32(const Call& c, double* acc, int row_first, int row_stride)
+{
+  typedef float T;
+  const Plan& p = c.plan;
+  double* damp = reinterpret_cast<double*>(c.ws + p.off_damp);
+  const long n_pad = (long)p.n_tiles * TILE;
+  const int in_plane = (c.flags & RMB_IN_PLANE) ? 1 : 0;
+  const bool wall = c.wall == RMB_SINGLE_WALL;
+  const bool per = c.L[0] > 0 || c.L[1] > 0;
+  const unsigned prep_blocks = (unsigned)((n_pad + 255) / 256);
+  if (c.block == RMB_UF_UT)
+    prepare_kernel<T, 2><<<prep_blocks, 256, 0, c.stream>>>(c.n_src, n_pad, c.r, c.va, c.vb, c.a, wall ? 1 : 0, per ? 0 : 1,
+                                                            in_plane, reinterpret_cast<SrcRec<T, 2>*>(c.ws), damp);
+  else
+    prepare_kernel<T, 1><<<prep_blocks, 256, 0, c.stream>>>(c.n_src, n_pad, c.r, c.va, c.vb, c.a, wall ? 1 : 0, per ? 0 : 1,
+                                                            in_plane, reinterpret_cast<SrcRec<T, 1>*>(c.ws), damp);
+  cudaError_t e = cudaMemsetAsync(acc, 0, (size_t)n_pad * 3 * sizeof(double), c.stream);
+  if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product (fp32): memset");
+  SymArgsT<T> A;
+  A.src = reinterpret_cast<const T*>(c.ws); A.acc = acc; A.n = c.n_src; A.n_tiles = p.n_tiles;
+  A.rows = 0; A.chunk = 1;
+  A.row_first = row_first; A.row_stride = row_stride;
+  A.K = make_uf_ctx<T>(T(0));
+  A.P.nbox = p.n_boxes;
+  for (int d = 0; d < 3; d++) {
+    A.P.per[d] = d < 2 && c.L[d] > 0;
+    A.P.L[d] = T(c.L[d]);
+    A.P.invL[d] = A.P.per[d] ? T(1.0 / c.L[d]) : T(0);
+  }
+  A.inva = T(1.0 / c.a);
+  A.box = make_box_table<T>(A.P, 1.0 / c.a);
+  const long rows_all = n_pad / (TPB * RMB_SYM_NT);
+  const long rows = (rows_all - row_first + row_stride - 1) / row_stride;
+  if (rows > 0) {
+    constexpr int NT = RMB_SYM_NT;
+    A.rows = (int)rows;
+    A.chunk = sym_chunk_for(rows, row_first, row_stride, TPB * NT, TILE, p.n_tiles, (long)sm_count() * RMB_SYM_RESIDENT,
+                            RMB_SYM_ITEMS, RMB_SYM_CHUNK_MIN, RMB_SYM_CHUNK_MAX);
+    const int gy = sym_grid_y(A.rows, row_first, row_stride, TPB * NT, TILE, p.n_tiles, A.chunk);
+    if (gy > 65535) return fail(RMB_E_ARG, "pair-symmetric product: too many chunks per row pair");
+    const dim3 grid((unsigned)((rows + 1) / 2), (unsigned)gy);
+#define RMB_SYM_LAUNCH32(B)                                                                     \
+    do {                                                                                        \
+      if (wall && per) sym_kernel<B, true, NT, true, true, T><<<grid, TPB, 0, c.stream>>>(A);     \
+      else if (wall) sym_kernel<B, true, NT, true, false, T><<<grid, TPB, 0, c.stream>>>(A);      \
+      else if (per) sym_kernel<B, true, NT, false, true, T><<<grid, TPB, 0, c.stream>>>(A);       \
+      else sym_kernel<B, true, NT, false, false, T><<<grid, TPB, 0, c.stream>>>(A);               \
+    } while (0)
+    if (c.block == RMB_UF_UT) {
+      RMB_SYM_LAUNCH32(UF_UT);
+    } else if (c.block == RMB_WT) {
+      RMB_SYM_LAUNCH32(WT);
+    } else if (c.block == RMB_UT || (c.block == RMB_WF && !wall)) {   // free space: WF is the same function as UT
+      RMB_SYM_LAUNCH32(UT);
+    } else if (c.block == RMB_WF) {
+      if (per) sym_kernel<WF, true, NT, true, true, T><<<grid, TPB, 0, c.stream>>>(A);
+      else sym_kernel<WF, true, NT, true, false, T><<<grid, TPB, 0, c.stream>>>(A);
+    } else {
+      RMB_SYM_LAUNCH32(UF);
+    }
+#undef RMB_SYM_LAUNCH32
+  }
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return fail_cuda(e, "pair-symmetric product (fp32): launch");
+  return 0;
+}
+
 int sym_partial(const Call& c, double* acc, int row_first, int row_stride)
 {
+  if (c.precision == RMB_FP32) return sym_partial_f32(c, acc, row_first, row_stride);
   const Plan& p = c.plan;
   double* damp = reinterpret_cast<double*>(c.ws + p.off_damp);
   const long n_pad = (long)p.n_tiles * TILE;

@@ -79,7 +79,9 @@ def test_static_workspace_matches_the_workspace_entry_point_twice_in_a_row(lib, 
 def test_static_workspace_fp32_and_deterministic_flag(lib):
     n = 20000
     r, f, t, a, eta = cloud(n, seed=9)
-    ref, out, _ = both(lib, UF, FP32, n, r, f, t, a, eta, None)
+    ref, out, _ = both(lib, UF, FP32, n, r, f, t, a, eta, None)            # default: fp32 pair-symmetric kernel (atomics)
+    assert relerr(out, ref) < 1e-6
+    ref, out, _ = both(lib, UF, FP32, n, r, f, t, a, eta, None, flags=8)   # RMB_DETERMINISTIC: fp32 row kernel
     assert torch.equal(out, ref)                              # the row kernel is bit-reproducible
     ref, out, _ = both(lib, UF, FP64, n, r, f, t, a, eta, None, flags=8)      # RMB_DETERMINISTIC
     assert torch.equal(out, ref)
