@@ -34,13 +34,13 @@ def test_every_block_pair_once(lib, n, world, nt):
     diag = np.zeros(nb, dtype=np.int32)
     info = np.zeros((world, 5), dtype=np.int32)
     ip = ctypes.POINTER(ctypes.c_int)
-    rc = lib.host_sym_schedule(n, world, nt, tpb, tile, 148 * 5, 128, 4, 16, sym.ctypes.data_as(ip),
+    rc = lib.host_sym_schedule(n, world, nt, tpb, tile, 148 * 5, 128, 1, 16, sym.ctypes.data_as(ip),
                                diag.ctypes.data_as(ip), info.ctypes.data_as(ip))
     assert rc == nb
     assert (diag == 1).all()
     assert (sym[np.triu_indices(nb, 1)] == 1).all() and (sym[np.tril_indices(nb)] == 0).all()
     active = info[:, 0] > 0
-    assert ((info[active, 2] >= 4) & (info[active, 2] <= 16)).all()
+    assert ((info[active, 2] >= 1) & (info[active, 2] <= 16)).all()
     if n == 20000:
         assert info[:, 3].min() > 1          # small launches are cut into several items
 
@@ -53,7 +53,7 @@ def test_items_are_equal_sized_and_the_grid_is_tight(lib, world):
     n, tile, tpb = 1000000, 256, 128
     info = np.zeros((world, 5), dtype=np.int32)
     ip = ctypes.POINTER(ctypes.c_int)
-    rc = lib.host_sym_schedule(n, world, 1, tpb, tile, 148 * 5, 128, 4, 16, None, None, info.ctypes.data_as(ip))
+    rc = lib.host_sym_schedule(n, world, 1, tpb, tile, 148 * 5, 128, 1, 16, None, None, info.ctypes.data_as(ip))
     assert rc > 0
     for gx, gy, chunk, items, tile_rows in info:
         assert items >= 0.97 * gx * gy
