@@ -531,7 +531,7 @@ def run_b200(args):
     from rigidmultiblobswall_b200 import parallel
     sm = parallel.ShardedMobility(r_d, eta, a, group=dist.group.WORLD if world > 1 else False,
                                   ranges=[(cuts[k], cuts[k + 1] - cuts[k]) for k in range(world)])
-    assert sm.symmetric or n < 13000
+    assert sm.symmetric or n < 8000
 
     def step():
         flush.zero_()                       # L2 flush between iterations (inside the timed region; ~0.1 ms)

@@ -65,7 +65,7 @@ extern "C" {
                              flag the symmetric kernel is still chosen for eligible calls with
                              n_sources >= RMB_SYMMETRIC_MIN_N */
 #define RMB_DETERMINISTIC 8 /* never use the pair-symmetric kernel: one thread per target, fixed summation order */
-#define RMB_SYMMETRIC_MIN_N 13000   /* measured r02h: row = symmetric at 12,000 blobs, symmetric +20 % at 15,000 */
+#define RMB_SYMMETRIC_MIN_N 8000    /* measured r02o (one-tile work items): row = symmetric at 6,000 blobs, symmetric +15 % at 8,000, +31 % at 12,000 */
 
 /* error codes */
 #define RMB_E_ARG (-1)        /* invalid argument                          */

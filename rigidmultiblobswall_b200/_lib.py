@@ -11,7 +11,7 @@ UF, UT, WF, WT, UF_UT = 0, 1, 2, 3, 4
 NO_WALL, SINGLE_WALL, FREE_SURFACE = 0, 1, 2
 FP64, FP32 = 0, 1
 IN_PLANE, NO_TMA, SYMMETRIC, DETERMINISTIC = 1, 2, 4, 8
-SYMMETRIC_MIN_N = 13000      # = RMB_SYMMETRIC_MIN_N (include/rmb_mobility.h)
+SYMMETRIC_MIN_N = 8000       # = RMB_SYMMETRIC_MIN_N (include/rmb_mobility.h)
 
 _lib = None
 

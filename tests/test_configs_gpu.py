@@ -116,7 +116,7 @@ def _brownian_step(n_shells, cg, noise_tol, vel_tol):
     ltol, gtol = cg[key + "/tolerances_lanczos_gmres"]
     system = parallel.ShardedRigidSystem(shell, loc, quat, eta, a, group=False)
     assert system.n_blobs_total == 162 * n_shells
-    if system.n_blobs_total >= 13000:
+    if system.n_blobs_total >= 8000:
         assert system.mobility.symmetric                      # the flagship (pair-symmetric) kernel is what runs
     z_d = torch.from_numpy(z).cuda()
     noise, it_l = system.stochastic_noise(z_d, factor=np.sqrt(2 * kT / dt), tolerance=ltol)
