@@ -49,6 +49,15 @@ namespace {
 #ifndef RMB_SYM_UNROLL
 #define RMB_SYM_UNROLL 1  // rotation-loop unroll of the pair-symmetric kernel
 #endif
+// Image-box loop of the pair-symmetric pseudo-periodic kernels (3 or 9 boxes).  Measured at config 3 (r02s,
+// profiles/r02s_box_unroll_ab.jsonl): unroll 3 costs the fp64 kernels registers (UF 368 -> 335 G pairs/s, fused 228 -> 213)
+// and gains the fp32 one 7 % (583 -> 624).
+#ifndef RMB_SYM_BOX_UNROLL
+#define RMB_SYM_BOX_UNROLL 1
+#endif
+#ifndef RMB_SYM_BOX_UNROLL_F32
+#define RMB_SYM_BOX_UNROLL_F32 3
+#endif
 #ifndef RMB_SYM_NT
 #define RMB_SYM_NT 1      // blobs per lane of the pair-symmetric kernel (1 or 2; TILE must be a multiple of 128 NT).
                           // Measured at N = 400k: 334.6 (1) vs 336.8 (2) G pairs/s, and 270 vs 252 at N = 20k
@@ -510,7 +519,8 @@ __device__ __forceinline__ void sym_block(const T* __restrict__ blk, int lane,
         else sym_pair<T, BLOCK, WALL, true>(rx, ry, rz, hi + hj, hi, hj, hi2, hi4, C, L.f[k], w + 3, any_near, r2, L.u[k], aj);
       } else {
         const T Rz = hi + hj, rz2 = rz * rz;
-#pragma unroll 1
+        constexpr int BU = F32 ? RMB_SYM_BOX_UNROLL_F32 : RMB_SYM_BOX_UNROLL;
+#pragma unroll BU
         for (int b = 0; b < A.box.n; b++) {
           const T bx = rx + A.box.s[b][0], by = ry + A.box.s[b][1];
           const T r2 = RMB_FMA(by, by, RMB_FMA(bx, bx, rz2));
