@@ -20,6 +20,7 @@ template <typename T>
 struct StTarget {
   T x, y, z;      // z already clamped to >= a in the wall form
   T a, a2, ia;    // radius, radius^2, 1/radius
+  T a_2, z_2;     // 2 radius, 2 z (loop invariants of the pair arithmetic)
 };
 
 // "is r2 <= s2 possible": conservative test on the high words only (off the
@@ -100,8 +101,8 @@ RMB_HD void rpy_radii(const StConsts<T>& K, T rx, T ry, T rz, T r2, T a, T ia, T
 //   ep = -2q - q^3 [ 2S/3 + (4P/3) t ]
 // S = a^2+b^2, P = a^2 b^2, W = a^2 y3 + b^2 x3, k = Z^2 t.
 template <typename T>
-RMB_HD void wall_radii(const StConsts<T>& K, T rx, T ry, T Z, T rxy2, T x3, T y3, T a2, T b2, T S, T fx, T fy, T fz,
-                       T& ux, T& uy, T& uz)
+RMB_HD void wall_radii(const StConsts<T>& K, T rx, T ry, T Z, T rxy2, T x3, T x3_2, T y3, T a2, T b2, T S, T fx, T fy,
+                       T fz, T& ux, T& uy, T& uz)
 {
   const T q = rsqrt_full(RMB_FMA(Z, Z, rxy2));
   const T t = q * q;
@@ -123,7 +124,7 @@ RMB_HD void wall_radii(const StConsts<T>& K, T rx, T ry, T Z, T rxy2, T x3, T y3
   be -= RMB_FMA(K.k6, xy, S);
   be = RMB_FMA(be, t, T(1.0));
   const T c20 = K.c203 * Pt * Zt;                              // (20P/3) Z t^2
-  const T ga = RMB_FMA(x3 + x3, RMB_FMA(dab, t, T(-1.0)), c20);
+  const T ga = RMB_FMA(x3_2, RMB_FMA(dab, t, T(-1.0)), c20);
   const T de = RMB_FMA(y3 + y3, RMB_FMA(-dab, t, T(-1.0)), c20);
   const T ep = -RMB_FMA(q3, RMB_FMA(K.c43, Pt, K.c23 * S), q + q);
   const T Rf = RMB_FMA(Z, fz, -RMB_FMA(ry, fy, rx * fx));
@@ -170,6 +171,7 @@ RMB_HD double st_target(bool wall, double x, double y, double z, double radius, 
   }
   t.x = T(x); t.y = T(y); t.z = T(z);
   t.a = T(radius); t.a2 = T(radius * radius); t.ia = T(1.0 / radius);
+  t.a_2 = T(2.0 * radius); t.z_2 = T(2.0 * z);
   return B;
 }
 
@@ -183,10 +185,9 @@ RMB_HD void pair_st(const StConsts<T>& K, const StTarget<T>& t, T rx, T ry, T rz
   const T r2 = RMB_FMA(rz, rz, rxy2);
   const T b2 = b * b;
   const T S = t.a2 + b2;
-  const T sab = t.a + b;
-  const T sab2 = sab * sab;
+  const T sab2 = RMB_FMA(t.a_2, b, S);          // (a + b)^2 = a^2 + b^2 + 2ab
   rpy_radii<T>(K, rx, ry, rz, r2, t.a, t.ia, b, ib, S, sab2, warp_any(maybe_le(r2, sab2)), fx, fy, fz, ux, uy, uz);
-  if (WALLMODE == ST_WALL) wall_radii<T>(K, rx, ry, Z, rxy2, t.z, y3, t.a2, b2, S, fx, fy, fz, ux, uy, uz);
+  if (WALLMODE == ST_WALL) wall_radii<T>(K, rx, ry, Z, rxy2, t.z, t.z_2, y3, t.a2, b2, S, fx, fy, fz, ux, uy, uz);
   if (WALLMODE == ST_FREE_SURFACE) {
     const T R2 = RMB_FMA(Z, Z, rxy2);
     rpy_radii<T>(K, rx, ry, Z, R2, t.a, t.ia, b, ib, S, sab2, warp_any(maybe_le(R2, sab2)), fx, fy, -fz, ux, uy, uz);
