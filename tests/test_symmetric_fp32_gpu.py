@@ -90,3 +90,28 @@ def test_default_selection_large(mb):
             out = mb.mobility_product(BLOCK_ID[blk], mb.SINGLE_WALL, r, f, eta, a, periodic_length=L, precision=mb.FP32)
             idx, orc = oracle_rows(blk, "single_wall", r, f, eta, a, L, seed=12)
             assert relerr(rows3(out, idx), orc) < TOL32, blk
+
+
+def test_deterministic_keyword_on_the_wrappers_and_the_sharded_product(mb):
+    """deterministic=True (an extra keyword of the *_b200 wrappers, and of parallel.ShardedMobility) keeps the
+    one-thread-per-target kernel: bit-reproducible run to run, fp64 and fp32, above the 8,000-blob threshold."""
+    from rigidmultiblobswall_b200 import parallel
+    rng = np.random.default_rng(8)
+    n, a, eta = 12000, 0.13, 7.0
+    side = (n * 4 * np.pi / 3 / 0.1) ** (1 / 3) * a
+    r = torch.from_numpy(side * rng.random((n, 3))).cuda()
+    f = torch.from_numpy(rng.standard_normal((n, 3))).cuda()
+    t = torch.from_numpy(rng.standard_normal((n, 3))).cuda()
+    for fn in (mb.single_wall_mobility_trans_times_force_b200, mb.single_wall_mobility_trans_times_force_b200_fp32,
+               mb.no_wall_mobility_rot_times_torque_b200):
+        d1, d2 = fn(r, f, eta, a, deterministic=True), fn(r, f, eta, a, deterministic=True)
+        assert torch.equal(d1, d2)
+        s = fn(r, f, eta, a)
+        assert not torch.equal(s, d1) and relerr(s, d1.cpu().numpy()) < (1e-5 if fn.__name__.endswith("fp32") else 1e-13)
+    d1 = mb.single_wall_mobility_trans_times_force_torque_b200(r, f, t, eta, a, deterministic=True)
+    assert torch.equal(d1, mb.single_wall_mobility_trans_times_force_torque_b200(r, f, t, eta, a, deterministic=True))
+    sm_d = parallel.ShardedMobility(r, eta, a, group=False, deterministic=True)
+    sm_s = parallel.ShardedMobility(r, eta, a, group=False)
+    assert not sm_d.symmetric and sm_s.symmetric
+    assert torch.equal(sm_d(f.reshape(-1)), sm_d(f.reshape(-1)))
+    assert relerr(sm_s(f.reshape(-1)), sm_d(f.reshape(-1)).cpu().numpy()) < 1e-13
